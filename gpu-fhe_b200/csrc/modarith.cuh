@@ -1,0 +1,103 @@
+// 64-bit modular arithmetic on the 32-bit integer datapath of sm_100a (IMAD / IMAD.WIDE /
+// IMAD.HI / IADD3).  No tensor cores: the NTT is not a dense contraction.
+//
+// Replaces the exact-integer semantics of /root/reference/arithmetic.py:3-13 ((a+b)%MOD,
+// (a-b)%MOD, (a*b)%MOD on dtype=object arrays) for residues stored as 64-bit words, and
+// supplies the butterfly arithmetic the reference's NTT/iNTT stubs (arithmetic.py:15-19)
+// never had.
+#pragma once
+#include <cstdint>
+
+namespace gfhe {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+// Per-limb constants, generated on the host (plan.cu) and resident in HBM.
+struct __align__(16) LimbParams {
+    u64 q;          // modulus, odd, < 2^62
+    u64 q2;         // 2q
+    u64 nq;         // -q mod 2^64
+    u64 bar_mu;     // floor(2^(k+63) / q), k = bit length of q  (single-mulhi Barrett)
+    u64 ninv;       // N^-1 mod q
+    u64 ninv_s;     // Shoup companion of ninv
+    u64 w1ninv;     // psi^-brv(1) * N^-1 mod q  (last inverse stage, N^-1 folded in)
+    u64 w1ninv_s;
+    u64 bar64;      // floor(2^64 / q): one-word Barrett for reducing arbitrary 64-bit inputs
+    u32 bar_shift;  // k - 1
+    u32 pad;
+};
+
+// x*w mod q up to a multiple of q: returns x*w - floor(x*ws/2^64)*q in [0, 2q) for ANY 64-bit x,
+// given ws = floor(w*2^64/q), w < q, and nq = -q mod 2^64.
+// 10 IMAD-class + 1 SEL (+1 zeroing move) in SASS: the exact high product uses
+// IMAD.HI / IMAD.WIDE with 64-bit accumulate, the low 64 bits of x*w + hi*nq are one
+// IMAD.WIDE chain plus four 32-bit IMADs into the top word.
+__device__ __forceinline__ u64 shoup_mul(u64 x, u64 w, u64 ws, u64 nq) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,wl,wh,pl,ph,nl,nh,t,h0,h1,top,lo;\n\t"
+        ".reg .u64 acc;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {wl,wh}, %2;\n\t"
+        "mov.b64 {pl,ph}, %3;\n\t"
+        "mov.b64 {nl,nh}, %4;\n\t"
+        // (h1:h0) = floor(x * ws / 2^64), exact
+        "mul.hi.u32 t, xl, pl;\n\t"
+        "mad.lo.cc.u32 t, xh, pl, t;\n\t"
+        "madc.hi.u32 h0, xh, pl, 0;\n\t"
+        "mad.lo.cc.u32 t, xl, ph, t;\n\t"
+        "madc.hi.cc.u32 h0, xl, ph, h0;\n\t"
+        "addc.u32 h1, 0, 0;\n\t"
+        "mad.lo.cc.u32 h0, xh, ph, h0;\n\t"
+        "madc.hi.u32 h1, xh, ph, h1;\n\t"
+        // r = x*w + h*nq  (mod 2^64)
+        "mul.wide.u32 acc, xl, wl;\n\t"
+        "mad.wide.u32 acc, h0, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, xl, wh, top;\n\t"
+        "mad.lo.u32 top, xh, wl, top;\n\t"
+        "mad.lo.u32 top, h0, nh, top;\n\t"
+        "mad.lo.u32 top, h1, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n"
+        : "=l"(r)
+        : "l"(x), "l"(w), "l"(ws), "l"(nq));
+    return r;
+}
+
+// x - c if x >= c else x, for x < 2^63 + c and c <= 2^63 (sign of the difference decides).
+// 5 SASS instructions: IADD3, IADD3.X, ISETP, SEL, SEL.
+__device__ __forceinline__ u64 csub(u64 x, u64 c) {
+    u64 d = x - c;
+    return (long long)d < 0 ? x : d;
+}
+
+__device__ __forceinline__ u64 mulhi64(u64 a, u64 b) { return __umul64hi(a, b); }
+
+// Full reduction of an arbitrary 64-bit value to [0, q) with the one-word Barrett constant.
+__device__ __forceinline__ u64 reduce64(u64 x, const LimbParams& P) {
+    u64 qh = mulhi64(x, P.bar64);        // floor(x/q) - 1 <= qh <= floor(x/q)
+    u64 r = x - qh * P.q;                 // in [0, 2q)
+    return csub(r, P.q);
+}
+
+// Signed 64-bit storage (torch.int64): Python's (v % q) for possibly negative v.
+__device__ __forceinline__ u64 reduce_signed(long long v, const LimbParams& P) {
+    if (v >= 0) return reduce64((u64)v, P);
+    u64 m = reduce64((u64)(-(v + 1)) + 1ull, P);   // |v| mod q without overflowing at INT64_MIN
+    return m == 0 ? 0 : P.q - m;
+}
+
+// a*b mod q, fully reduced, for a, b < q < 2^62 (single-mulhi Barrett, quotient error <= 2).
+__device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, const LimbParams& P) {
+    u64 z0 = a * b, z1 = mulhi64(a, b);
+    u32 s = P.bar_shift;                                   // k - 1, 0 < s < 64 for q >= 2
+    u64 x = (z0 >> s) | (z1 << (64 - s));                  // floor(z / 2^(k-1)) < 2^(k+1)
+    u64 qh = mulhi64(x, P.bar_mu);
+    u64 r = z0 - qh * P.q;                                 // in [0, 3q)
+    r = csub(r, P.q2);
+    return csub(r, P.q);
+}
+
+}  // namespace gfhe

@@ -1,0 +1,131 @@
+// Plan construction: twiddle and Shoup-companion tables are generated ONCE on the host from the
+// primitive 2N-th roots that primitive.py found, uploaded, and stay resident in HBM.
+//
+// The reference has no such code (/root/reference/primitive.py:3-4 is a placeholder); the
+// table layout is dictated by the kernels in ntt_kernels.cu:
+//   fwd[l][k] = { psi_l^brv(k),  floor(psi_l^brv(k)  * 2^64 / q_l) }   k in [1, N)
+//   inv[l][k] = { psi_l^-brv(k), floor(psi_l^-brv(k) * 2^64 / q_l) }
+// brv = bit reversal over log2(N) bits, so stage "m groups" reads entries [m, 2m) contiguously.
+#include <cstdlib>
+#include <thread>
+#include <vector>
+#include "plan.h"
+
+namespace gfhe {
+
+typedef unsigned __int128 u128;
+
+static inline u64 h_mulmod(u64 a, u64 b, u64 q) { return (u64)((u128)a * b % q); }
+static u64 h_powmod(u64 b, u64 e, u64 q) {
+    u64 r = 1 % q;
+    b %= q;
+    for (; e; e >>= 1) {
+        if (e & 1) r = h_mulmod(r, b, q);
+        b = h_mulmod(b, b, q);
+    }
+    return r;
+}
+static inline u64 h_shoup(u64 w, u64 q) { return (u64)(((u128)w << 64) / q); }
+static inline u32 h_brv(u32 k, u32 bits) {
+    u32 r = 0;
+    for (u32 i = 0; i < bits; ++i) { r = (r << 1) | (k & 1); k >>= 1; }
+    return r;
+}
+
+static void fill_limb_params(LimbParams& P, u64 q, u32 logN, u64 psi) {
+    P = LimbParams{};
+    P.q = q;
+    P.q2 = 2 * q;
+    P.nq = 0 - q;
+    u32 k = 64 - (u32)__builtin_clzll(q);             // bit length
+    P.bar_shift = k - 1;
+    u128 mu = ((u128)1 << (k + 63)) / q;               // < 2^64 unless q is a power of two
+    P.bar_mu = mu >> 64 ? ~0ull : (u64)mu;
+    P.bar64 = (u64)((((u128)1) << 64) / q);
+    if (logN) {
+        const u64 N = 1ull << logN;
+        P.ninv = h_powmod(N % q, q - 2, q);
+        P.ninv_s = h_shoup(P.ninv, q);
+        const u64 psi_inv = h_powmod(psi, 2 * N - 1, q);
+        const u64 w1 = h_powmod(psi_inv, N >> 1, q);   // psi^-brv(1) = psi^-(N/2)
+        P.w1ninv = h_mulmod(w1, P.ninv, q);
+        P.w1ninv_s = h_shoup(P.w1ninv, q);
+    }
+}
+
+// Sequential powers psi^0..psi^(N-1), scattered to bit-reversed positions.
+static void fill_tables(ulonglong2* fwd, ulonglong2* inv, u64 q, u32 logN, u64 psi) {
+    const u64 N = 1ull << logN;
+    const u64 psi_inv = h_powmod(psi, 2 * N - 1, q);
+    u64 pw = 1, pwi = 1;
+    for (u64 e = 0; e < N; ++e) {
+        const u32 k = h_brv((u32)e, logN);
+        fwd[k] = make_ulonglong2(pw, h_shoup(pw, q));
+        inv[k] = make_ulonglong2(pwi, h_shoup(pwi, q));
+        pw = h_mulmod(pw, psi, q);
+        pwi = h_mulmod(pwi, psi_inv, q);
+    }
+}
+
+int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi) {
+    if (!out || !moduli || L == 0) return -1;
+    if (logN != 0 && (logN < 4 || logN > 20 || !psi)) return -2;
+    for (u32 l = 0; l < L; ++l) {
+        const u64 q = moduli[l];
+        if (q < 2 || q >= (1ull << 62)) return -3;
+        if (logN) {
+            const u64 N = 1ull << logN;
+            if ((q & 1) == 0 || (q - 1) % (2 * N) != 0) return -4;           // need q = 1 mod 2N
+            if (h_powmod(psi[l], N, q) != q - 1) return -5;                   // psi^N = -1
+        }
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return (int)e;
+    Plan* pl = new Plan();
+    pl->device = device; pl->logN = logN; pl->L = L;
+
+    std::vector<LimbParams> hp(L);
+    for (u32 l = 0; l < L; ++l) fill_limb_params(hp[l], moduli[l], logN, logN ? psi[l] : 0);
+    if ((e = cudaMalloc(&pl->d_params, sizeof(LimbParams) * L)) != cudaSuccess) { plan_destroy(pl); return (int)e; }
+    if ((e = cudaMemcpy(pl->d_params, hp.data(), sizeof(LimbParams) * L, cudaMemcpyHostToDevice)) != cudaSuccess) { plan_destroy(pl); return (int)e; }
+
+    if (logN) {
+        const size_t N = (size_t)1 << logN, bytes = sizeof(ulonglong2) * N * L;
+        ulonglong2 *hf = nullptr, *hi = nullptr;
+        hf = (ulonglong2*)std::malloc(bytes); hi = (ulonglong2*)std::malloc(bytes);
+        if (!hf || !hi) { std::free(hf); std::free(hi); plan_destroy(pl); return -6; }
+        unsigned nthr = std::thread::hardware_concurrency();
+        if (nthr == 0) nthr = 1;
+        if (nthr > L) nthr = L;
+        if (nthr > 32) nthr = 32;
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < nthr; ++t)
+            pool.emplace_back([=]() {
+                for (u32 l = t; l < L; l += nthr) fill_tables(hf + l * N, hi + l * N, moduli[l], logN, psi[l]);
+            });
+        for (auto& th : pool) th.join();
+        e = cudaMalloc(&pl->d_fwd, bytes);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv, bytes);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd, hf, bytes, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv, hi, bytes, cudaMemcpyHostToDevice);
+        std::free(hf); std::free(hi);
+        if (e != cudaSuccess) { plan_destroy(pl); return (int)e; }
+    }
+    *out = pl;
+    return 0;
+}
+
+void host_pipe_destroy(Plan* p);   // capi.cu
+
+int plan_destroy(Plan* p) {
+    if (!p) return 0;
+    cudaSetDevice(p->device);
+    host_pipe_destroy(p);
+    if (p->d_params) cudaFree(p->d_params);
+    if (p->d_fwd) cudaFree(p->d_fwd);
+    if (p->d_inv) cudaFree(p->d_inv);
+    delete p;
+    return 0;
+}
+
+}  // namespace gfhe

@@ -1,0 +1,34 @@
+// Host-side plan: per-limb constants and twiddle tables, generated once on the host from the
+// primitive 2N-th roots supplied by primitive.py and kept resident in HBM.
+#pragma once
+#include <cuda_runtime.h>
+#include "modarith.cuh"
+
+namespace gfhe {
+
+struct Plan {
+    int device = 0;
+    u32 logN = 0;                      // 0: modulus set only (vec_* ops), no tables
+    u32 L = 0;
+    LimbParams* d_params = nullptr;    // [L]
+    ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
+    ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
+    void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
+};
+
+// plan.cu
+int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi);
+int plan_destroy(Plan* p);
+
+// ntt_kernels.cu -- all operate on limbs [limb0, limb0 + nl) of the plan; buffers are [nl, B, N]
+cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
+cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
+cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
+                            cudaStream_t st);
+size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B);
+
+// vec_kernels.cu
+cudaError_t launch_vec_op(int op, const Plan& pl, u32 limb0, u32 nl, const long long* a, const long long* b,
+                          long long* out, u64 inner, cudaStream_t st);
+
+}  // namespace gfhe

@@ -1,0 +1,95 @@
+/*
+ * gpufhe_b200 -- C ABI of the B200-native negacyclic-NTT / RNS polynomial-multiplication path.
+ *
+ * This is the drop-in boundary for GPU-FHE's polynomial-ring hot path.  The reference has no
+ * FFI of its own (it is three pure-Python modules); each entry point below is the native
+ * implementation behind one reference-level Python function, which keeps its signature in
+ * arithmetic.py / primitive.py / polynomial.py at the repo root:
+ *
+ *   gfhe_vec_add / _sub / _mul   <- /root/reference/arithmetic.py:3-5, :7-9, :11-13
+ *   gfhe_ntt_forward             <- /root/reference/arithmetic.py:15-16  (NTT, an identity stub there)
+ *   gfhe_ntt_inverse             <- /root/reference/arithmetic.py:18-19  (iNTT, an identity stub there)
+ *   gfhe_plan_create             <- /root/reference/primitive.py:3-4     (placeholder for the roots of unity)
+ *   gfhe_poly_mul                <- /root/reference/" polynomial.py":3-5 (module that would hold poly_mul)
+ *   gfhe_*_host                  <- the same calls made with host (numpy) arrays, as the reference's
+ *                                   callers would make them; copies are pipelined inside the call
+ *
+ * Conventions: plain pointers and sizes only; all device pointers are raw CUDA device addresses
+ * (e.g. torch.Tensor.data_ptr()); `stream` is a cudaStream_t passed as void* (NULL = legacy
+ * default stream); work is enqueued asynchronously unless the name ends in _host.  Every function
+ * returns 0 on success, a negative GFHE_E* code for argument errors, or a positive cudaError_t.
+ * No exception crosses this boundary.  The caller owns every buffer; the library owns only plans.
+ *
+ * Data layout: residues are 64-bit words, canonical tensor layout [L, B, N] -- limb outermost,
+ * N contiguous -- so one limb's batch is one contiguous block.  NTT(x)[k] = x(psi^(2*brv(k)+1)):
+ * forward output is in bit-reversed evaluation order, inverse output is natural order in [0, q).
+ */
+#ifndef GPUFHE_B200_H
+#define GPUFHE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GFHE_ABI_VERSION 1
+
+#define GFHE_EARG      (-1)   /* null pointer / zero size */
+#define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
+#define GFHE_EMODULUS  (-3)   /* modulus outside [2, 2^62) */
+#define GFHE_ENOTNTT   (-4)   /* modulus is not 1 mod 2N */
+#define GFHE_EROOT     (-5)   /* psi^N != -1 mod q */
+#define GFHE_ENOMEM    (-6)
+#define GFHE_ERANGE    (-7)   /* limb range outside the plan */
+#define GFHE_EWORKSPACE (-8)  /* workspace missing or too small */
+#define GFHE_ENOTABLES (-9)   /* plan was created without NTT tables (log2_n == 0) */
+
+typedef struct gfhe_plan* gfhe_plan_t;   /* opaque; one per (device, N, modulus chain) */
+
+int gfhe_abi_version(void);
+const char* gfhe_error_string(int code);
+
+/* Build per-limb constants and, if log2_n != 0, twiddle + Shoup tables (generated on the host
+ * from psi[l], a primitive 2N-th root of unity mod moduli[l]) and upload them to `device`.
+ * log2_n == 0 creates a modulus set usable by gfhe_vec_* only (psi may be NULL). */
+int gfhe_plan_create(gfhe_plan_t* out, int device, uint32_t log2_n, uint32_t num_limbs,
+                     const uint64_t* moduli, const uint64_t* psi);
+int gfhe_plan_destroy(gfhe_plan_t plan);
+int gfhe_plan_info(gfhe_plan_t plan, int* device, uint32_t* log2_n, uint32_t* num_limbs);
+
+/* Batched transforms over limbs [limb0, limb0 + num_limbs) of the plan; buffers are
+ * [num_limbs, batch, N].  in == out is allowed.  Forward expects residues in [0, q). */
+int gfhe_ntt_forward(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                     const uint64_t* d_in, uint64_t* d_out, void* stream);
+int gfhe_ntt_inverse(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                     const uint64_t* d_in, uint64_t* d_out, void* stream);
+
+/* c = a * b in Z_q[X]/(X^N + 1) per limb, coefficient domain in and out, as one fused pipeline
+ * (pointwise product and N^-1 folded into the adjacent NTT stages).  c may alias neither a nor b.
+ * N > 4096 needs a device workspace of gfhe_poly_mul_workspace_bytes(). */
+size_t gfhe_poly_mul_workspace_bytes(gfhe_plan_t plan, uint32_t num_limbs, uint32_t batch);
+int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                  const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_c,
+                  void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* out = (a op b) mod q_l, exact for ANY int64 inputs (Python % semantics, result in [0, q)).
+ * Buffers are [num_limbs, inner]; limb l of the range uses modulus limb0 + l. */
+int gfhe_vec_add(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                 const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
+int gfhe_vec_sub(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                 const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
+int gfhe_vec_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                 const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
+
+/* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan
+ * (pinned memory gives full PCIe rate; pageable works).  Limb groups are streamed
+ * H2D -> kernels -> D2H on separate streams so copies overlap compute.  Synchronous. */
+int gfhe_ntt_host(gfhe_plan_t plan, int inverse, uint32_t batch, const uint64_t* h_in, uint64_t* h_out);
+int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUFHE_B200_H */

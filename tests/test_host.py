@@ -1,0 +1,117 @@
+"""CPU suite, part 3: host-side logic of the drop-in modules (no GPU)."""
+import inspect
+
+import numpy as np
+import pytest
+
+
+def test_drop_in_surface_matches_reference(built_lib):
+    # the seven reference callables with their exact positional signatures
+    import arithmetic
+    import polynomial
+    import primitive
+    want = {"vec_add": ["a", "b", "MOD"], "vec_sub": ["a", "b", "MOD"], "vec_mul": ["a", "b", "MOD"],
+            "NTT": ["x"], "iNTT": ["x"], "XXX": [], "poly_add": ["a", "b", "MOD"]}
+    for name, params in want.items():
+        fn = getattr(polynomial, name)
+        positional = [p.name for p in inspect.signature(fn).parameters.values()
+                      if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+        assert positional == params, name
+    # star-import chain: every lower name is exported by every module above it (incl. the leaked np)
+    ns = {}
+    exec("from polynomial import *", ns)
+    for name in list(want) + ["np", "poly_mul"]:
+        assert name in ns
+    ns = {}
+    exec("from primitive import *", ns)
+    assert "poly_add" not in ns and "XXX" in ns and "NTT" in ns
+    assert arithmetic.np is np and primitive.vec_add is arithmetic.vec_add
+
+
+def test_xxx_prints_xxx(built_lib, capsys):
+    import primitive
+    assert primitive.XXX() is None
+    assert capsys.readouterr().out == "XXX\n"       # /root/reference/primitive.py:3-4
+
+
+def test_roots_and_primes(built_lib):
+    import primitive as P
+    from oracle import oracle as O
+    for q, N in [(1073479681, 1024), (1125899902124033, 4096), (1152921504606584833, 65536)]:
+        psi = P.find_psi(q, N)
+        assert psi == O.find_psi(q, N)                # product code and oracle agree on the convention
+        assert pow(psi, N, q) == q - 1
+    assert P.ntt_primes(60, 3) == O.ntt_primes(60, 3)
+    assert P.ntt_primes(30, 1, N=1024) == [1073707009]    # largest 30-bit prime = 1 mod 2048
+    with pytest.raises(ValueError):
+        P.find_psi(101, 16)
+    assert P.is_probable_prime(1152921504606584833) and not P.is_probable_prime(1152921504606584833 - 4)
+
+
+def test_ring_context(built_lib):
+    import primitive as P
+    from gpu_fhe_b200 import ring
+    assert P.get_ring() is None
+    with pytest.raises(RuntimeError):
+        ring.resolve_moduli(None)                      # NTT(x) with no ring: clear error, no identity fallback
+    with P.ring([97, 193]):
+        assert ring.resolve_moduli(None) == (97, 193)
+        with P.ring(np.array([[257]])):
+            assert P.get_ring() == (257,)
+        assert P.get_ring() == (97, 193)
+    assert P.get_ring() is None
+    assert ring.resolve_moduli(np.array([5, 7], dtype=object).reshape(2, 1, 1)) == (5, 7)
+    assert ring.resolve_moduli(12289) == (12289,)
+
+
+def test_shape_and_modulus_mapping(built_lib):
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import dispatch as d
+    assert d._lbn((4, 16, 64), 4) == (4, 16, 64)
+    assert d._lbn((16, 64), 1) == (1, 16, 64)
+    assert d._lbn((64,), 1) == (1, 1, 64)
+    assert d._lbn((2, 3, 5, 64), 2) == (2, 15, 64)
+    with pytest.raises(ValueError):
+        d._lbn((3, 64), 2)
+    assert d._vec_moduli(7, (2, 3, 4)) == ((7,), 24)
+    assert d._vec_moduli(np.array([[[5]], [[7]]], dtype=object), (2, 3, 4)) == ((5, 7), 12)
+    assert d._vec_moduli(np.array([5, 7]), (2,)) == ((5, 7), 1)
+    with pytest.raises(ValueError):          # numpy would broadcast (2,) against the LAST axis
+        d._vec_moduli(np.array([5, 7]), (2, 3, 2))
+
+
+def test_no_cpu_fallback(built_lib):
+    import torch
+
+    import polynomial as P
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    a = np.arange(16, dtype=np.int64)
+    for call in (lambda: P.vec_add(a, a, 97), lambda: P.NTT(a, MOD=97), lambda: P.poly_mul(a, a, 97)):
+        with pytest.raises(RuntimeError, match="no CPU fallback"):
+            call()
+    with pytest.raises(AssertionError):     # shape mismatch: bare AssertionError like arithmetic.py:4
+        P.vec_add(np.arange(4), np.arange(5), 7)
+
+
+def test_partition():
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import shard
+    # config 4 on 8 GPUs: 4 limbs x 16 batch each;  config 3 on 2 GPUs: 4 limbs each
+    s = [shard.partition(32, 16, 8, r) for r in range(8)]
+    assert all(x.g_l == 8 and x.g_b == 1 and x.num_limbs == 4 and x.num_batch == 16 for x in s)
+    assert [x.limbs for x in s] == [(4 * r, 4 * r + 4) for r in range(8)]
+    s = [shard.partition(8, 128, 2, r) for r in range(2)]
+    assert [x.limbs for x in s] == [(0, 4), (4, 8)]
+    # fewer limbs than ranks: split the batch too
+    s = [shard.partition(2, 8, 8, r) for r in range(8)]
+    assert all(x.g_l == 2 and x.g_b == 4 for x in s)
+    cover = set()
+    for x in s:
+        for l in range(*x.limbs):
+            for b in range(*x.batch):
+                assert (l, b) not in cover
+                cover.add((l, b))
+    assert len(cover) == 16
+    with pytest.raises(ValueError):
+        shard.partition(1, 3, 2, 0)

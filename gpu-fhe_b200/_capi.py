@@ -33,6 +33,9 @@ SYMBOLS = {
     "gfhe_vec_mul": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),
     "gfhe_poly_mul_host": (ctypes.c_int, [vp, u32, vp, vp, vp]),
+    "gfhe_profile_enable": (ctypes.c_int, [vp, ctypes.c_int]),
+    "gfhe_profile_read": (ctypes.c_int, [vp, u32, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_double),
+                                         ctypes.POINTER(ctypes.c_uint64)]),
 }
 
 

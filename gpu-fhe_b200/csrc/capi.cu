@@ -64,6 +64,43 @@ int gfhe_plan_info(gfhe_plan_t plan, int* device, uint32_t* log2_n, uint32_t* nu
     return 0;
 }
 
+int gfhe_profile_enable(gfhe_plan_t plan, int on) {
+    if (!plan) return GFHE_EARG;
+    Plan* pl = P(plan);
+    if (!pl->prof) pl->prof = new Profiler();
+    pl->prof->on = on != 0;
+    return 0;
+}
+
+static const char* const kKernelNames[K_COUNT] = {"k_col_fwd", "k_row_fwd", "k_row_inv", "k_col_inv", "k_row_polymul", "k_vec"};
+
+int gfhe_profile_read(gfhe_plan_t plan, uint32_t max_kernels, const char** names, double* total_ms, uint64_t* launches) {
+    if (!plan) return GFHE_EARG;
+    Plan* pl = P(plan);
+    if (!pl->prof) return 0;
+    DeviceGuard g(pl->device);
+    double ms[K_COUNT] = {};
+    uint64_t cnt[K_COUNT] = {};
+    for (auto& r : pl->prof->recs) {
+        cudaError_t e = cudaEventSynchronize(r.b);
+        if (e != cudaSuccess) return -(int)e;
+        float t = 0.f;
+        if ((e = cudaEventElapsedTime(&t, r.a, r.b)) != cudaSuccess) return -(int)e;
+        ms[r.kid] += t; cnt[r.kid] += 1;
+        pl->prof->pool.push_back(r.a); pl->prof->pool.push_back(r.b);
+    }
+    pl->prof->recs.clear();
+    uint32_t n = 0;
+    for (int k = 0; k < K_COUNT && n < max_kernels; ++k) {
+        if (!cnt[k]) continue;
+        if (names) names[n] = kKernelNames[k];
+        if (total_ms) total_ms[n] = ms[k];
+        if (launches) launches[n] = cnt[k];
+        ++n;
+    }
+    return (int)n;
+}
+
 int gfhe_ntt_forward(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
                      const uint64_t* d_in, uint64_t* d_out, void* stream) {
     if (int rc = check_range(P(plan), limb0, nl)) return rc;

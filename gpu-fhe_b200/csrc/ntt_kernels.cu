@@ -240,19 +240,19 @@ cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64
     const unsigned nslab = slabs_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: k_row_fwd<LS><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0); break;
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<LS><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0); } break;
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
     } else {
         switch (24 - (int)pl.logN) {
-#define X(LC) case LC: k_col_fwd<LC><<<dim3(nslab, 1), 256, 0, st>>>(in, out, nullptr, nullptr, pl.d_fwd, pl.d_params, B, limb0); break;
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nslab, 1), 256, 0, st>>>(in, out, nullptr, nullptr, pl.d_fwd, pl.d_params, B, limb0); } break;
             GFHE_COL_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
-        k_row_fwd<12><<<nslab, 256, 0, st>>>(out, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0);
+        { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<12><<<nslab, 256, 0, st>>>(out, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0); }
     }
     return cudaGetLastError();
 }
@@ -261,15 +261,15 @@ cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64
     const unsigned nslab = slabs_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: k_row_inv<LS, true><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0); break;
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<LS, true><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0); } break;
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
     } else {
-        k_row_inv<12, false><<<nslab, 256, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0);
+        { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<12, false><<<nslab, 256, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0); }
         switch (24 - (int)pl.logN) {
-#define X(LC) case LC: k_col_inv<LC><<<nslab, 256, 0, st>>>(out, out, pl.d_inv, pl.d_params, B, limb0); break;
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nslab, 256, 0, st>>>(out, out, pl.d_inv, pl.d_params, B, limb0); } break;
             GFHE_COL_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
@@ -289,7 +289,7 @@ static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, c
         if (e != cudaSuccess) return e;
         configured[dev] = true;
     }
-    k_row_polymul<LOGS, WHOLE><<<nslab, RowGeo<LOGS>::NT, smem, st>>>(a, b, c, pl.d_fwd, pl.d_inv, pl.d_params, pl.logN, B, limb0);
+    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<LOGS, WHOLE><<<nslab, RowGeo<LOGS>::NT, smem, st>>>(a, b, c, pl.d_fwd, pl.d_inv, pl.d_params, pl.logN, B, limb0); }
     return cudaGetLastError();
 }
 
@@ -311,7 +311,7 @@ cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, con
     if (!ws) return cudaErrorInvalidValue;
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
     switch (24 - (int)pl.logN) {
-#define X(LC) case LC: k_col_fwd<LC><<<dim3(nslab, 2), 256, 0, st>>>(a, c, b, ws, pl.d_fwd, pl.d_params, B, limb0); break;
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nslab, 2), 256, 0, st>>>(a, c, b, ws, pl.d_fwd, pl.d_params, B, limb0); } break;
         GFHE_COL_CASES(X)
 #undef X
         default: return cudaErrorInvalidValue;
@@ -319,7 +319,7 @@ cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, con
     cudaError_t e = launch_row_polymul<12, false>(pl, limb0, c, ws, c, B, nslab, st);
     if (e != cudaSuccess) return e;
     switch (24 - (int)pl.logN) {
-#define X(LC) case LC: k_col_inv<LC><<<nslab, 256, 0, st>>>(c, c, pl.d_inv, pl.d_params, B, limb0); break;
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nslab, 256, 0, st>>>(c, c, pl.d_inv, pl.d_params, B, limb0); } break;
         GFHE_COL_CASES(X)
 #undef X
         default: return cudaErrorInvalidValue;

@@ -121,6 +121,11 @@ int plan_destroy(Plan* p) {
     if (!p) return 0;
     cudaSetDevice(p->device);
     host_pipe_destroy(p);
+    if (p->prof) {
+        for (auto& r : p->prof->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        for (auto e : p->prof->pool) cudaEventDestroy(e);
+        delete p->prof;
+    }
     if (p->d_params) cudaFree(p->d_params);
     if (p->d_fwd) cudaFree(p->d_fwd);
     if (p->d_inv) cudaFree(p->d_inv);

@@ -2,9 +2,24 @@
 // primitive 2N-th roots supplied by primitive.py and kept resident in HBM.
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include "modarith.cuh"
 
 namespace gfhe {
+
+// Optional per-kernel timing (gfhe_profile_enable): every launch is bracketed by cudaEvents on
+// its own stream, so bench.py can report each kernel's live duration and share of the step.
+enum KernelId { K_COL_FWD = 0, K_ROW_FWD, K_ROW_INV, K_COL_INV, K_ROW_POLYMUL, K_VEC, K_COUNT };
+struct Profiler {
+    bool on = false;
+    struct Rec { int kid; cudaEvent_t a, b; };
+    std::vector<Rec> recs;
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get() {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+};
 
 struct Plan {
     int device = 0;
@@ -14,6 +29,19 @@ struct Plan {
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
+    Profiler* prof = nullptr;
+};
+
+struct ProfScope {
+    Profiler* p; cudaStream_t st; size_t idx;
+    ProfScope(const Plan& pl, int kid, cudaStream_t s) : p(pl.prof && pl.prof->on ? pl.prof : nullptr), st(s), idx(0) {
+        if (!p || p->recs.size() >= 65536) { p = nullptr; return; }
+        Profiler::Rec r{kid, p->get(), p->get()};
+        cudaEventRecord(r.a, st);
+        idx = p->recs.size();
+        p->recs.push_back(r);
+    }
+    ~ProfScope() { if (p) cudaEventRecord(p->recs[idx].b, st); }
 };
 
 // plan.cu

@@ -55,6 +55,7 @@ static cudaError_t launch_vec(const Plan& pl, u32 limb0, u32 nl, const long long
     if (per_row > need) per_row = need;
     if (per_row < 1) per_row = 1;
     dim3 grid((unsigned)per_row, nl);
+    ProfScope ps(pl, K_VEC, st);
     if (vec2) k_vec<OP, true><<<grid, 256, 0, st>>>(a, b, out, pl.d_params, inner, limb0);
     else      k_vec<OP, false><<<grid, 256, 0, st>>>(a, b, out, pl.d_params, inner, limb0);
     return cudaGetLastError();

@@ -89,6 +89,14 @@ int gfhe_vec_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t 
 int gfhe_ntt_host(gfhe_plan_t plan, int inverse, uint32_t batch, const uint64_t* h_in, uint64_t* h_out);
 int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c);
 
+/* Measurement hook (bench.py): when enabled, every kernel launched through `plan` is bracketed
+ * by cudaEvents on its stream.  gfhe_profile_read waits for them, writes up to max_kernels
+ * (kernel name, summed milliseconds, launch count) triples and returns how many it wrote
+ * (>= 0); a negative return is an error (GFHE_E*, or -cudaError_t). */
+int gfhe_profile_enable(gfhe_plan_t plan, int on);
+int gfhe_profile_read(gfhe_plan_t plan, uint32_t max_kernels, const char** names, double* total_ms,
+                      uint64_t* launches);
+
 #ifdef __cplusplus
 }
 #endif

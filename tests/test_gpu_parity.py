@@ -1,0 +1,362 @@
+"""GPU parity tests (run with -m gpu on the B200 box).  Everything goes through the drop-in modules
+(arithmetic / primitive / polynomial) or straight through the C ABI; the oracle is the checker only.
+Bar: bit-exact.  /root/reference is not read here: its outputs live in tests/golden/*.npz.
+"""
+import ctypes
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cref
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def dev_i64(a: np.ndarray, device) -> torch.Tensor:
+    return torch.from_numpy(np.ascontiguousarray(a).view(np.int64)).to(device)
+
+
+def host_u64(t: torch.Tensor) -> np.ndarray:
+    return t.cpu().numpy().view(np.uint64)
+
+
+def rand_lbn(seed, moduli, B, N):
+    rng = np.random.default_rng(seed)
+    return np.stack([rng.integers(0, q, (B, N), dtype=np.uint64) for q in moduli])
+
+
+def oracle_ring(N, moduli):
+    return cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli])
+
+
+def col(moduli):
+    return np.array(list(moduli), dtype=object).reshape(len(moduli), 1, 1)
+
+
+# ---------------------------------------------------------------------------------------------------
+# element-wise ops vs the REFERENCE's own outputs (golden) -- arithmetic.py:3-13
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("op", ["vec_add", "vec_sub", "vec_mul"])
+def test_vec_ops_match_reference_golden(cuda_device, golden_dir, op):
+    import arithmetic
+    g = np.load(golden_dir + "/vec_ops.npz")
+    for name in g["names"]:
+        a, b, mod = g[name + "_a"], g[name + "_b"], g[name + "_mod"]
+        want = g[name + "_" + op]
+        MOD = col(int(m) for m in mod)
+        got = getattr(arithmetic, op)(dev_i64(a, cuda_device), dev_i64(b, cuda_device), MOD)
+        assert got.is_cuda and got.dtype == torch.int64 and tuple(got.shape) == a.shape
+        assert np.array_equal(host_u64(got), want), (op, name)
+        # numpy in -> numpy out (host buffers through the same kernels), object dtype preserved
+        got_np = getattr(arithmetic, op)(a.astype(object), b.astype(object), MOD)
+        assert got_np.dtype == object and [int(v) for v in got_np.ravel()] == want.ravel().tolist()
+
+
+def test_vec_ops_shapes_and_edges(cuda_device):
+    import arithmetic as A
+    q = 1152921504606584833
+    # scalar MOD, 1-D, odd length, unaligned views, empty
+    for n in (0, 1, 2, 3, 255, 4097):
+        rng = np.random.default_rng(n)
+        a, b = rng.integers(0, q, n, dtype=np.uint64), rng.integers(0, q, n, dtype=np.uint64)
+        for op in ("add", "sub", "mul"):
+            got = getattr(A, "vec_" + op)(dev_i64(a, cuda_device), dev_i64(b, cuda_device), q)
+            assert np.array_equal(host_u64(got), cref.vec_op(op, a, b, q)), (n, op)
+    # a non-contiguous / offset view must not be assumed 16-byte aligned
+    base = torch.arange(0, 2 * 1001, device=cuda_device, dtype=torch.int64)
+    v = base[1::2]
+    got = A.vec_add(v, v, 97)
+    assert torch.equal(got, (2 * v) % 97)
+    # inputs are never modified (out-of-place like the reference)
+    x = dev_i64(np.arange(64, dtype=np.uint64), cuda_device)
+    x0 = x.clone()
+    A.vec_mul(x, x, 97)
+    assert torch.equal(x, x0)
+    # uint64 tensors are accepted as containers
+    u = x.view(torch.uint64)
+    assert A.vec_add(u, u, 97).dtype == torch.uint64
+    with pytest.raises(AssertionError):
+        A.vec_add(x, x[:-1], 97)
+
+
+def test_poly_add_returns_both_sums(cuda_device):
+    import polynomial as P
+    q = 1125899902124033
+    rng = np.random.default_rng(5)
+    a = [rng.integers(0, q, (2, 64), dtype=np.uint64) for _ in range(2)]
+    b = [rng.integers(0, q, (2, 64), dtype=np.uint64) for _ in range(2)]
+    ta = tuple(dev_i64(x, cuda_device) for x in a)
+    tb = tuple(dev_i64(x, cuda_device) for x in b)
+    s = P.poly_add(ta, tb, q)     # " polynomial.py":3-5 drops these; we return them
+    d = P.poly_sub(ta, tb, q)
+    for i in range(2):
+        assert np.array_equal(host_u64(s[i]), cref.vec_op("add", a[i], b[i], q))
+        assert np.array_equal(host_u64(d[i]), cref.vec_op("sub", a[i], b[i], q))
+
+
+# ---------------------------------------------------------------------------------------------------
+# transforms vs the definition-level golden vectors and the oracle
+# ---------------------------------------------------------------------------------------------------
+def test_ntt_matches_definition_golden(cuda_device, golden_dir):
+    import arithmetic as A
+    g = np.load(golden_dir + "/ntt_small.npz")
+    for name in g["names"]:
+        q, psi = (int(v) for v in g[name + "_q"])
+        x, X = g[name + "_x"], g[name + "_X"]
+        got = A.NTT(dev_i64(x, cuda_device), MOD=q)
+        assert np.array_equal(host_u64(got), X), name
+        back = A.iNTT(got, MOD=q)
+        assert np.array_equal(host_u64(back), x), name
+
+
+@pytest.mark.parametrize("logn", list(range(4, 18)))
+def test_ntt_intt_all_sizes(cuda_device, logn):
+    """Every kernel instantiation: N = 2^4 .. 2^17, 2 limbs x 3 batch, 60-bit primes."""
+    import primitive as P
+    N = 1 << logn
+    moduli = P.ntt_primes(60, 2)
+    x = rand_lbn(logn, moduli, 3, N)
+    # extreme residues
+    x[:, 0, 0] = 0
+    x[0, 0, 1] = moduli[0] - 1
+    x[1, 1, :] = moduli[1] - 1
+    R = oracle_ring(N, moduli)
+    tx = dev_i64(x, cuda_device)
+    with P.ring(moduli):
+        X = P.NTT(tx)
+        back = P.iNTT(X)
+    assert np.array_equal(host_u64(X), R.ntt(x, fast=True, nthreads=4))
+    assert torch.equal(back, tx)
+    assert torch.equal(tx, dev_i64(x, cuda_device))          # input untouched
+    # evaluation order, independent of any table: NTT(x)[k] = x(psi^(2 brv(k)+1))
+    rng = random.Random(logn)
+    Xh = host_u64(X)
+    for _ in range(2 if logn > 12 else 4):
+        l, b, k = rng.randrange(2), rng.randrange(3), rng.randrange(N)
+        assert int(Xh[l, b, k]) == O.ntt_point(x[l, b].tolist(), moduli[l], O.find_psi(moduli[l], N), k)
+
+
+@pytest.mark.parametrize("logn", [18, 20])
+def test_ntt_roundtrip_large(cuda_device, logn):
+    import primitive as P
+    N = 1 << logn
+    moduli = P.ntt_primes(60, 1, N=N)
+    x = rand_lbn(logn, moduli, 1, N)
+    tx = dev_i64(x, cuda_device)
+    with P.ring(moduli):
+        X = P.NTT(tx)
+        assert torch.equal(P.iNTT(X), tx)
+    R = oracle_ring(N, moduli)
+    assert np.array_equal(host_u64(X), R.ntt(x, fast=True))
+
+
+@pytest.mark.parametrize("bits", [30, 50, 61])
+def test_modulus_widths(cuda_device, bits):
+    """30-bit (config 1), 50-bit (config 2) and the widest supported (61-bit) primes."""
+    import primitive as P
+    N = 2048
+    moduli = P.ntt_primes(bits, 2)
+    a, b = rand_lbn(1, moduli, 2, N), rand_lbn(2, moduli, 2, N)
+    a[:, :, :8] = np.array(moduli, dtype=np.uint64).reshape(2, 1, 1) - 1
+    R = oracle_ring(N, moduli)
+    import polynomial as Poly
+    c = Poly.poly_mul(dev_i64(a, cuda_device), dev_i64(b, cuda_device), list(moduli))
+    assert np.array_equal(host_u64(c), R.poly_mul(a, b, fast=True))
+
+
+def test_in_place_and_limb_ranges_through_c_abi(cuda_device):
+    """Straight C-ABI calls: in == out, and a limb sub-range of a plan (what a limb shard uses)."""
+    import primitive as P
+    from gpu_fhe_b200 import _capi
+    N, B = 8192, 2
+    moduli = P.ntt_primes(60, 4)
+    plan = P.make_plan(N, moduli, device=cuda_device.index)
+    x = rand_lbn(9, moduli, B, N)
+    R = oracle_ring(N, moduli)
+    want = R.ntt(x)
+    t = dev_i64(x, cuda_device)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = _capi.lib.gfhe_ntt_forward(plan.handle, 0, 4, B, t.data_ptr(), t.data_ptr(), st)       # in place
+    assert rc == 0
+    assert np.array_equal(host_u64(t), want)
+    # limbs [1, 3) only, buffers hold just those two limbs
+    sub = dev_i64(x[1:3], cuda_device)
+    out = torch.empty_like(sub)
+    assert _capi.lib.gfhe_ntt_forward(plan.handle, 1, 2, B, sub.data_ptr(), out.data_ptr(), st) == 0
+    assert np.array_equal(host_u64(out), want[1:3])
+    back = torch.empty_like(sub)
+    assert _capi.lib.gfhe_ntt_inverse(plan.handle, 1, 2, B, out.data_ptr(), back.data_ptr(), st) == 0
+    assert torch.equal(back, sub)
+    # argument errors
+    assert _capi.lib.gfhe_ntt_forward(plan.handle, 3, 2, B, sub.data_ptr(), out.data_ptr(), st) == -7
+    need = _capi.lib.gfhe_poly_mul_workspace_bytes(plan.handle, 2, B)
+    assert need == 2 * B * N * 8
+    assert _capi.lib.gfhe_poly_mul(plan.handle, 1, 2, B, sub.data_ptr(), sub.data_ptr(), out.data_ptr(), None, 0, st) == -8
+    assert _capi.lib.gfhe_poly_mul(plan.handle, 1, 2, B, sub.data_ptr(), sub.data_ptr(), sub.data_ptr(), None, 0, st) == -1
+    torch.cuda.synchronize()
+
+
+# ---------------------------------------------------------------------------------------------------
+# poly-mul: golden products (schoolbook / Kronecker), properties, BASELINE configs
+# ---------------------------------------------------------------------------------------------------
+def test_poly_mul_matches_golden_products(cuda_device, golden_dir):
+    import polynomial as P
+    g = np.load(golden_dir + "/polymul.npz")
+    for name in g["names"]:
+        q = int(g[name + "_q"][0])
+        a, b, c = g[name + "_a"], g[name + "_b"], g[name + "_c"]
+        got = P.poly_mul(dev_i64(a, cuda_device), dev_i64(b, cuda_device), q)
+        assert np.array_equal(host_u64(got), c), name
+        got_np = P.poly_mul(a, b, q)                 # host arrays in, host array out
+        assert isinstance(got_np, np.ndarray) and np.array_equal(got_np.view(np.uint64), c), name
+
+
+@pytest.mark.parametrize("logn", [4, 6, 9, 12, 13, 15, 16, 17])
+def test_poly_mul_properties(cuda_device, logn):
+    import polynomial as P
+    N = 1 << logn
+    moduli = P.ntt_primes(60, 2)
+    a, b, c2 = rand_lbn(1, moduli, 2, N), rand_lbn(2, moduli, 2, N), rand_lbn(3, moduli, 2, N)
+    ta, tb, tc = (dev_i64(v, cuda_device) for v in (a, b, c2))
+    MOD = col(moduli)
+    with P.ring(moduli):
+        ab = P.poly_mul(ta, tb)
+        # oracle
+        assert np.array_equal(host_u64(ab), oracle_ring(N, moduli).poly_mul(a, b, fast=True, nthreads=4))
+        # commutative
+        assert torch.equal(ab, P.poly_mul(tb, ta))
+        # identity: a * 1 = a
+        one = torch.zeros_like(ta)
+        one[:, :, 0] = 1
+        assert torch.equal(P.poly_mul(ta, one), ta)
+        # a * X = negacyclic shift with sign flip
+        xp = torch.zeros_like(ta)
+        xp[:, :, 1] = 1
+        sh = host_u64(P.poly_mul(ta, xp))
+        for l, q in enumerate(moduli):
+            want = np.concatenate([(q - a[l, :, -1:]) % q, a[l, :, :-1]], axis=1)
+            assert np.array_equal(sh[l], want)
+        # distributive: a*(b+c) = a*b + a*c
+        lhs = P.poly_mul(ta, P.vec_add(tb, tc, MOD))
+        rhs = P.vec_add(ab, P.poly_mul(ta, tc), MOD)
+        assert torch.equal(lhs, rhs)
+        # NTT is linear and multiplicative: NTT(a*b) = NTT(a) . NTT(b)
+        assert torch.equal(P.NTT(ab), P.vec_mul(P.NTT(ta), P.NTT(tb), MOD))
+
+
+def test_config1_n1024_30bit(cuda_device):
+    """BASELINE config 1: N=1024 NTT->INTT round trip + poly-mul, one 30-bit prime, [1,1,1024]."""
+    import polynomial as P
+    q, N = 1073479681, 1024
+    assert P.find_psi(q, N) == 530309095
+    rng = np.random.default_rng(20261104 + 1)
+    a, b = rng.integers(0, q, N, dtype=np.uint64), rng.integers(0, q, N, dtype=np.uint64)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    X = P.NTT(ta, MOD=q)
+    assert host_u64(X).tolist() == O.ntt_definition(a.tolist(), q, 530309095)
+    assert torch.equal(P.iNTT(X, MOD=q), ta)
+    c = P.poly_mul(ta, tb, q)
+    assert host_u64(c).tolist() == O.schoolbook_negacyclic(a.tolist(), b.tolist(), q)
+
+
+def test_config2_n4096_4x50bit_batch256(cuda_device):
+    """BASELINE config 2: [4,256,4096], 50-bit primes -- full-array comparison."""
+    import polynomial as P
+    N, B = 4096, 256
+    moduli = P.ntt_primes(50, 4)
+    assert moduli[0] == 1125899902124033
+    a, b = rand_lbn(20261104 + 2, moduli, B, N), rand_lbn(99, moduli, B, N)
+    c = P.poly_mul(dev_i64(a, cuda_device), dev_i64(b, cuda_device), list(moduli))
+    assert np.array_equal(host_u64(c), oracle_ring(N, moduli).poly_mul(a, b, fast=True, nthreads=16))
+    # independent of every NTT: Kronecker substitution on a sample
+    ch = host_u64(c)
+    for (l, bi) in [(0, 0), (3, 255)]:
+        assert ch[l, bi].tolist() == O.kronecker_negacyclic(a[l, bi].tolist(), b[l, bi].tolist(), moduli[l])
+
+
+def test_config3_n16384_8limbs_batch128(cuda_device):
+    """BASELINE config 3: [8,128,16384] NTT and INTT."""
+    import primitive as P
+    N, B = 16384, 128
+    moduli = P.ntt_primes(60, 8)
+    x = rand_lbn(20261104 + 3, moduli, B, N)
+    tx = dev_i64(x, cuda_device)
+    with P.ring(moduli):
+        X = P.NTT(tx)
+        back = P.iNTT(X)
+    assert torch.equal(back, tx)
+    assert np.array_equal(host_u64(X), oracle_ring(N, moduli).ntt(x, fast=True, nthreads=16))
+
+
+def test_config4_n65536_32x60bit_batch16(cuda_device):
+    """BASELINE config 4 at full size: [32,16,65536] poly-mul, 60-bit primes.
+
+    Full-array comparison against the C oracle (fast flavour, itself pinned to the exact flavour and
+    to Kronecker in the CPU suite), plus size-independent checks: one Kronecker product, the paired
+    point-evaluation / schoolbook-coefficient spot checks on every limb."""
+    import polynomial as P
+    N, L, B = 65536, 32, 16
+    moduli = P.ntt_primes(60, L)
+    assert moduli[0] == 1152921504606584833
+    a, b = rand_lbn(20261104 + 4, moduli, B, N), rand_lbn(77, moduli, B, N)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    c = P.poly_mul(ta, tb, list(moduli))
+    ch = host_u64(c)
+    want = oracle_ring(N, moduli).poly_mul(a, b, fast=True, nthreads=32)
+    assert np.array_equal(ch, want)
+    assert ch[0, 0].tolist() == O.kronecker_negacyclic(a[0, 0].tolist(), b[0, 0].tolist(), moduli[0])
+    rng = random.Random(4)
+    for l in range(L):
+        bi, k = rng.randrange(B), rng.randrange(N)
+        psi = O.find_psi(moduli[l], N)
+        al, bl, cl = a[l, bi].tolist(), b[l, bi].tolist(), ch[l, bi].tolist()
+        assert O.check_point_eval(al, bl, cl, moduli[l], psi, k)
+        assert O.schoolbook_coeff(al, bl, moduli[l], k) == cl[k]
+
+
+def test_host_entry_points(cuda_device):
+    """gfhe_poly_mul_host / gfhe_ntt_host: host arrays, copies pipelined over limb groups."""
+    import arithmetic  # noqa: F401
+    import primitive as P
+    from gpu_fhe_b200 import dispatch
+    N, L, B = 16384, 6, 40            # 5 MiB per limb -> several limb groups, last one ragged
+    moduli = P.ntt_primes(60, L)
+    a, b = rand_lbn(1, moduli, B, N), rand_lbn(2, moduli, B, N)
+    R = oracle_ring(N, moduli)
+    out = np.empty_like(a)
+    dispatch.poly_mul_host(a, b, out, moduli, device=cuda_device.index)
+    assert np.array_equal(out, R.poly_mul(a, b, fast=True, nthreads=16))
+    X = np.empty_like(a)
+    dispatch.ntt_host(a, X, moduli, device=cuda_device.index)
+    assert np.array_equal(X, R.ntt(a, fast=True, nthreads=16))
+    back = np.empty_like(a)
+    dispatch.ntt_host(X, back, moduli, inverse=True, device=cuda_device.index)
+    assert np.array_equal(back, a)
+    # pinned host memory path
+    pa = torch.from_numpy(a.view(np.int64)).pin_memory()
+    pb = torch.from_numpy(b.view(np.int64)).pin_memory()
+    pc = torch.empty_like(pa).pin_memory()
+    dispatch.poly_mul_host(pa.numpy().view(np.uint64), pb.numpy().view(np.uint64), pc.numpy().view(np.uint64), moduli,
+                           device=cuda_device.index)
+    assert np.array_equal(pc.numpy().view(np.uint64), out)
+
+
+def test_sharded_equals_unsharded(cuda_device):
+    """Limb/batch shards computed independently (as each rank would) reassemble to the full result."""
+    import polynomial as P
+    from gpu_fhe_b200 import shard
+    N, L, B = 8192, 4, 4
+    moduli = P.ntt_primes(60, L)
+    a, b = rand_lbn(1, moduli, B, N), rand_lbn(2, moduli, B, N)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    full = P.poly_mul(ta, tb, list(moduli))
+    for world in (2, 4, 8):
+        out = torch.empty_like(full)
+        for r in range(world):
+            sh = shard.partition(L, B, world, r)
+            part = P.poly_mul(shard.take(ta, sh), shard.take(tb, sh), list(moduli[sh.limbs[0]:sh.limbs[1]]))
+            out[sh.limbs[0]:sh.limbs[1], sh.batch[0]:sh.batch[1]] = part
+        assert torch.equal(out, full), world

@@ -290,7 +290,8 @@ def run_b200(args, rank, world, local_rank):
         dispatch.poly_mul_host(a_np, b_np, c_np, moduli, device=local_rank)
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    assert np.array_equal(c_np[0, 0], dc[0, 0].cpu().numpy().view(np.uint64))
+    if rank == 0:
+        assert np.array_equal(c_np[0, 0], want[0, 0]), "e2e (host-buffer) result is not bit-exact"
 
     # ---- the one collective: all-gather of result limbs to every rank (reported apart)
     gather_ms = None

@@ -46,7 +46,7 @@ def test_vec_ops_match_reference_golden(cuda_device, golden_dir, op):
     for name in g["names"]:
         a, b, mod = g[name + "_a"], g[name + "_b"], g[name + "_mod"]
         want = g[name + "_" + op]
-        MOD = col(int(m) for m in mod)
+        MOD = col([int(m) for m in mod])
         got = getattr(arithmetic, op)(dev_i64(a, cuda_device), dev_i64(b, cuda_device), MOD)
         assert got.is_cuda and got.dtype == torch.int64 and tuple(got.shape) == a.shape
         assert np.array_equal(host_u64(got), want), (op, name)

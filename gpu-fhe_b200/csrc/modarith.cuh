@@ -90,14 +90,17 @@ __device__ __forceinline__ u64 reduce_signed(long long v, const LimbParams& P) {
 }
 
 // a*b mod q, fully reduced, for a, b < q < 2^62 (single-mulhi Barrett, quotient error <= 2).
-__device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, const LimbParams& P) {
+// s = k - 1 (k = bit length of q), mu = floor(2^(k+63) / q).
+__device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, u64 q, u64 mu, u32 s) {
     u64 z0 = a * b, z1 = mulhi64(a, b);
-    u32 s = P.bar_shift;                                   // k - 1, 0 < s < 64 for q >= 2
     u64 x = (z0 >> s) | (z1 << (64 - s));                  // floor(z / 2^(k-1)) < 2^(k+1)
-    u64 qh = mulhi64(x, P.bar_mu);
-    u64 r = z0 - qh * P.q;                                 // in [0, 3q)
-    r = csub(r, P.q2);
-    return csub(r, P.q);
+    u64 qh = mulhi64(x, mu);
+    u64 r = z0 - qh * q;                                   // in [0, 3q)
+    r = csub(r, 2 * q);
+    return csub(r, q);
+}
+__device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, const LimbParams& P) {
+    return barrett_mul(a, b, P.q, P.bar_mu, P.bar_shift);
 }
 
 }  // namespace gfhe

@@ -1,11 +1,17 @@
 // sm_100a kernels for batched negacyclic NTT / INTT / fused polynomial multiplication over
 // RNS limbs, layout [L, B, N] (limb outermost, N contiguous), 8-byte residues.
 //
-// N <= 4096 : one kernel, one CTA per limb-polynomial (the slab is the polynomial).
-// N  > 4096 : N = N1 x 4096.  "column" kernel = the log2(N1) high stages on stride-4096
-//             columns (twiddles shared by every column), "row" kernel = the 12 low stages on
-//             contiguous 4096-residue rows.  poly-mul fuses  row-fwd(a), row-fwd(b), pointwise
-//             product and row-inv into ONE kernel, so no element-wise kernel ever runs.
+// Work unit: a TILE of 4096 residues on one 256-thread CTA (16 residues per thread in registers,
+// four radix-2 stages per "round", rounds joined by an XOR-swizzled shared-memory exchange).
+//
+// N <= 4096 : one kernel, one CTA per limb-polynomial (the tile is the polynomial).
+// N  > 4096 : two passes, N = 2^T x 2^S with S = 8 (N <= 2^16) or 12 (N <= 2^20), T = log2 N - S <= 8.
+//             "column" pass = the T high stages: tile = 2^T rows (stride 2^S) x 2^(12-T) contiguous
+//             columns, twiddles shared by every tile.  "row" pass = the S low stages on a contiguous
+//             tile (16 independent 256-point sub-transforms when S = 8).  For N = 2^16 this is the
+//             balanced 8 + 8 split: each pass does 8 stages per 16 bytes of traffic.
+//             poly-mul fuses row-fwd(a), row-fwd(b), the pointwise product and row-inv into ONE
+//             kernel, so no element-wise kernel ever runs; N^-1 is folded into the last inverse stage.
 //
 // These kernels are what arithmetic.NTT / arithmetic.iNTT / polynomial.poly_mul dispatch to;
 // they replace the stubs at /root/reference/arithmetic.py:15-19 and the missing product in
@@ -16,68 +22,82 @@
 namespace gfhe {
 
 // ------------------------------------------------------------------------------------------------
-// row kernels: contiguous slab of 2^LOGS residues, LOGS = min(log2 N, 12)
+// row kernels: LOGS low stages on a contiguous tile of 2^LOGT residues (LOGS <= LOGT <= 12)
 // ------------------------------------------------------------------------------------------------
-template <int LOGS>
-struct RowGeo {
-    static constexpr int NT = LOGS > 4 ? (1 << (LOGS - 4)) : 1;
+template <int LOGT>
+struct TileGeo {
+    static constexpr int NT = LOGT > 4 ? (1 << (LOGT - 4)) : 1;
+    static constexpr int MINB = LOGT == 12 ? 2 : 1;   // 256-thread CTAs: cap at 128 registers
 };
 
-struct SlabId {
-    u64 g0;     // flat offset of the slab in the [L,B,N] array
-    u32 off;    // offset of the slab inside its polynomial
+struct Tables {   // kernel argument: the plan's device tables
+    const ulonglong2* tw;    // [L][N]
+    const ulonglong2* t0;    // [L][15][N/16]
+    const LimbParams* params;
+};
+
+struct TileId {
+    u64 g0;     // flat offset of the tile in the [L,B,N] array
+    u32 off;    // offset of the tile inside its polynomial
     u32 limb;
 };
-template <int LOGS>
-__device__ __forceinline__ SlabId slab_id(u32 logN, u32 B, u32 limb0) {
-    SlabId s;
-    s.g0 = (u64)blockIdx.x << LOGS;
+template <int LOGT>
+__device__ __forceinline__ TileId tile_id(u32 logN, u32 B, u32 limb0) {
+    TileId s;
+    s.g0 = (u64)blockIdx.x << LOGT;
     const u32 p = (u32)(s.g0 >> logN);
     s.off = (u32)s.g0 & ((1u << logN) - 1u);
     s.limb = limb0 + p / B;
     return s;
 }
+__device__ __forceinline__ TwTab limb_tables(const Tables& T, u32 limb, u32 logN) {
+    const size_t N = (size_t)1 << logN;
+    return TwTab{T.tw + limb * N, T.t0 + limb * (15 * (N >> 4)), (u32)N};
+}
 
-template <int LOGS>
+template <int LOGT>
 __device__ __forceinline__ void copy_out_swizzled(const u64* sm, u64* out, u32 tid) {
-    constexpr int NT = RowGeo<LOGS>::NT;
+    constexpr int NT = TileGeo<LOGT>::NT;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
         const u32 e = 2u * (it * NT + tid);
         *reinterpret_cast<ulonglong2*>(out + e) = *reinterpret_cast<const ulonglong2*>(sm + swz(e));
     }
 }
-template <int LOGS>
+template <int LOGT>
 __device__ __forceinline__ void copy_in_swizzled(u64* sm, const u64* in, u32 tid) {
-    constexpr int NT = RowGeo<LOGS>::NT;
-    ulonglong2 v[8];
+    constexpr int NT = TileGeo<LOGT>::NT;
 #pragma unroll
-    for (int it = 0; it < 8; ++it) v[it] = *reinterpret_cast<const ulonglong2*>(in + 2u * (it * NT + tid));
+    for (int h = 0; h < 2; ++h) {   // two batches of four 16-byte loads in flight
+        ulonglong2 v[4];
 #pragma unroll
-    for (int it = 0; it < 8; ++it) *reinterpret_cast<ulonglong2*>(sm + swz(2u * (it * NT + tid))) = v[it];
+        for (int it = 0; it < 4; ++it) v[it] = *reinterpret_cast<const ulonglong2*>(in + 2u * ((4 * h + it) * NT + tid));
+#pragma unroll
+        for (int it = 0; it < 4; ++it) *reinterpret_cast<ulonglong2*>(sm + swz(2u * ((4 * h + it) * NT + tid))) = v[it];
+    }
 }
 
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
-template <int LOGS>
-__global__ void __launch_bounds__(RowGeo<LOGS>::NT)
-k_row_fwd(const u64* in, u64* out, const ulonglong2* __restrict__ twf,
-          const LimbParams* __restrict__ params, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[1 << LOGS];
+template <int LOGS, int LOGT>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+    __shared__ __align__(16) u64 sm[1 << LOGT];
     const u32 tid = threadIdx.x;
-    const SlabId s = slab_id<LOGS>(logN, B, limb0);
-    const LimbParams P = params[s.limb];
-    const ulonglong2* tw = twf + ((size_t)s.limb << logN);
+    const TileId s = tile_id<LOGT>(logN, B, limb0);
+    const LimbParams* __restrict__ Pg = tabs.params + s.limb;
+    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const TwTab T = limb_tables(tabs, s.limb, logN);
     u64 r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm, tid, tw, (1u << logN) + s.off, P.q2, P.nq);
+    slab_fwd<LOGS>(r, sm, tid, T, s.off, q2, nq);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], P.q2), P.q);
-    if constexpr (LOGS > 4) {
+    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], q2), q2 >> 1);
+    if constexpr (LOGT > 4) {
         sm_store<0>(sm, tid, r);   // own 128-byte row: no hazard with the preceding sm_load<0>
         __syncthreads();
-        copy_out_swizzled<LOGS>(sm, out + s.g0, tid);
+        copy_out_swizzled<LOGT>(sm, out + s.g0, tid);
     } else {
 #pragma unroll
         for (int i = 0; i < kElems; ++i) out[s.g0 + i] = r[i];
@@ -85,211 +105,234 @@ k_row_fwd(const u64* in, u64* out, const ulonglong2* __restrict__ twf,
 }
 
 // Inverse: the LOGS low stages (bottom first).  Always the first pass of an inverse NTT; when the
-// slab is the whole polynomial it also folds N^-1 and fully reduces.
-template <int LOGS, bool WHOLE>
-__global__ void __launch_bounds__(RowGeo<LOGS>::NT)
-k_row_inv(const u64* in, u64* out, const ulonglong2* __restrict__ twi,
-          const LimbParams* __restrict__ params, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[1 << LOGS];
+// tile is the whole polynomial it also folds N^-1 and fully reduces.
+template <int LOGS, int LOGT, bool WHOLE>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+    __shared__ __align__(16) u64 sm[1 << LOGT];
     const u32 tid = threadIdx.x;
-    const SlabId s = slab_id<LOGS>(logN, B, limb0);
-    const LimbParams P = params[s.limb];
-    const ulonglong2* tw = twi + ((size_t)s.limb << logN);
+    const TileId s = tile_id<LOGT>(logN, B, limb0);
+    const LimbParams* __restrict__ Pg = tabs.params + s.limb;
+    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const TwTab T = limb_tables(tabs, s.limb, logN);
     u64 r[kElems];
-    if constexpr (LOGS > 4) {
-        copy_in_swizzled<LOGS>(sm, in + s.g0, tid);
+    if constexpr (LOGT > 4) {
+        copy_in_swizzled<LOGT>(sm, in + s.g0, tid);
         __syncthreads();
         sm_load<0>(sm, tid, r);
     } else {
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + i];
     }
-    slab_inv<LOGS, WHOLE>(r, sm, tid, tw, (1u << logN) + s.off, P);
+    slab_inv<LOGS, WHOLE>(r, sm, tid, T, s.off, q2, nq, Pg);
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) out[s.g0 + elem_index<P0>(tid, i)] = r[i];
 }
 
-// Fused product on a slab: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
+// Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
 // is the complete negacyclic product of one limb-polynomial in a single launch.
-template <int LOGS, bool WHOLE>
-__global__ void __launch_bounds__(RowGeo<LOGS>::NT)
-k_row_polymul(const u64* a, const u64* b, u64* c,
-              const ulonglong2* __restrict__ twf, const ulonglong2* __restrict__ twi,
-              const LimbParams* __restrict__ params, u32 logN, u32 B, u32 limb0) {
+template <int LOGS, int LOGT, bool WHOLE>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
     extern __shared__ __align__(16) u64 smem[];
     u64* sm0 = smem;                 // exchange buffer
-    u64* sm1 = smem + (1 << LOGS);   // stash for NTT(a) while NTT(b) is computed
+    u64* sm1 = smem + (1 << LOGT);   // stash for NTT(a) while NTT(b) is computed
     const u32 tid = threadIdx.x;
-    const SlabId s = slab_id<LOGS>(logN, B, limb0);
-    const LimbParams P = params[s.limb];
-    const ulonglong2* tf = twf + ((size_t)s.limb << logN);
-    const ulonglong2* ti = twi + ((size_t)s.limb << logN);
-    const u32 G = (1u << logN) + s.off;
+    const TileId s = tile_id<LOGT>(logN, B, limb0);
+    const LimbParams* __restrict__ Pg = tf.params + s.limb;
+    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const TwTab Tf = limb_tables(tf, s.limb, logN);
+    const TwTab Ti = limb_tables(ti, s.limb, logN);
     constexpr int P0 = Sched<LOGS>::p0(0);
     u64 r[kElems];
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = a[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm0, tid, tf, G, P.q2, P.nq);
+    slab_fwd<LOGS>(r, sm0, tid, Tf, s.off, q2, nq);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], P.q2), P.q);
-    sm_store<0>(sm1, tid, r);
-    __syncthreads();   // every thread has finished reading a's last exchange out of sm0
+    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], q2), q2 >> 1);
+    sm_store<0>(sm1, tid, r);   // private 128-byte row of sm1: written and read back by this thread only
+    __syncthreads();            // every thread has finished reading a's last exchange out of sm0
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = b[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm0, tid, tf, G, P.q2, P.nq);
-    {
-        u64 ra[kElems];
-        sm_load<0>(sm1, tid, ra);
+    slab_fwd<LOGS>(r, sm0, tid, Tf, s.off, q2, nq);
+    const u64 q = q2 >> 1, mu = __ldg(&Pg->bar_mu);
+    const u32 bs = __ldg(&Pg->bar_shift);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = barrett_mul(ra[i], csub(csub(r[i], P.q2), P.q), P);
+    for (int j = 0; j < 8; ++j) {
+        const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sm1 + swz((tid << 4) | (2 * j)));
+        r[2 * j] = barrett_mul(va.x, csub(csub(r[2 * j], q2), q), q, mu, bs);
+        r[2 * j + 1] = barrett_mul(va.y, csub(csub(r[2 * j + 1], q2), q), q, mu, bs);
     }
-    slab_inv<LOGS, WHOLE>(r, sm0, tid, ti, G, P);
+    slab_inv<LOGS, WHOLE>(r, sm0, tid, Ti, s.off, q2, nq, Pg);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) c[s.g0 + elem_index<P0>(tid, i)] = r[i];
 }
 
 // ------------------------------------------------------------------------------------------------
-// column kernels (N > 4096): slab = N1 rows x C columns, N1 = 2^(12-LOGC), C = 2^LOGC; slab index
-// e = k*C + j  <->  coefficient k*4096 + tile*C + j.  Transform bits of e: [LOGC, 12).
+// column kernels (N > 4096): tile = 2^T rows x C columns, T = 12 - LOGC, C = 2^LOGC, row stride 2^S;
+// tile index e = k*C + j  <->  coefficient k*2^S + tile*C + j.  Transform bits of e: [LOGC, 12).
+// Twiddles depend only on the row bits, so every tile of a limb reads the same 2^T - 1 entries.
 // ------------------------------------------------------------------------------------------------
 template <int LOGC>
 struct ColGeo {
     static constexpr int LO8 = LOGC > 8 ? LOGC - 8 : 0;   // lowest local bit of the window at bit 8
     static constexpr int LO4 = LOGC > 4 ? LOGC - 4 : 0;   // lowest local bit of the window at bit 4
     static constexpr bool TWO = LOGC < 8;                  // needs the second window
-    __device__ static __forceinline__ u64 addr(u64 base, u32 e) {
-        return base + (e & ((1u << LOGC) - 1u)) + ((u64)(e >> LOGC) << kMaxLogSlab);
+    __device__ static __forceinline__ u64 addr(u64 base, u32 e, u32 S) {
+        return base + (e & ((1u << LOGC) - 1u)) + ((u64)(e >> LOGC) << S);
     }
 };
+struct ColId { u64 base; u32 limb; };
+template <int LOGC>
+__device__ __forceinline__ ColId col_id(u32 S, u32 B, u32 limb0) {
+    const u32 logN = S + 12 - LOGC, lt = S - LOGC;          // 2^lt tiles per polynomial
+    const u32 p = blockIdx.x >> lt, tile = blockIdx.x & ((1u << lt) - 1u);
+    return ColId{((u64)p << logN) + ((u64)tile << LOGC), limb0 + p / B};
+}
 
 template <int LOGC>
-__global__ void __launch_bounds__(256)
-k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1,
-          const ulonglong2* __restrict__ twf, const LimbParams* __restrict__ params, u32 B, u32 limb0) {
+__global__ void __launch_bounds__(256, 2)
+k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 S, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC>;
-    constexpr u32 logN = 24 - LOGC;
     __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
     const u64* in = blockIdx.y ? in1 : in0;
     u64* out = blockIdx.y ? out1 : out0;
     const u32 tid = threadIdx.x;
-    const u32 p = blockIdx.x >> (12 - LOGC), tile = blockIdx.x & ((1u << (12 - LOGC)) - 1u);
-    const u64 base = ((u64)p << logN) + ((u64)tile << LOGC);
-    const u32 limb = limb0 + p / B;
-    const LimbParams P = params[limb];
-    const ulonglong2* tw = twf + ((size_t)limb << logN);
+    const ColId id = col_id<LOGC>(S, B, limb0);
+    const LimbParams* __restrict__ Pg = tabs.params + id.limb;
+    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << (S + 12 - LOGC));
     u64 r[kElems];
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(base, elem_index<8>(tid, i))];
-    fwd_round<3, Geo::LO8>(r, tw, 1u, P.q2, P.nq);
+    for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<8>(tid, i), S)];
+    fwd_round<3, Geo::LO8>(r, TwStd{tw, 1u}, q2, nq);
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
         __syncthreads();
         sm_load<4>(sm, tid, r);
-        fwd_round<3, Geo::LO4>(r, tw, 16u + (tid >> 4), P.q2, P.nq);
+        fwd_round<3, Geo::LO4>(r, TwStd{tw, 16u + (tid >> 4)}, q2, nq);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) out[Geo::addr(base, elem_index<4>(tid, i))] = r[i];
+        for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<4>(tid, i), S)] = r[i];
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) out[Geo::addr(base, elem_index<8>(tid, i))] = r[i];
+        for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<8>(tid, i), S)] = r[i];
     }
 }
 
 template <int LOGC>
-__global__ void __launch_bounds__(256)
-k_col_inv(const u64* in, u64* out, const ulonglong2* __restrict__ twi,
-          const LimbParams* __restrict__ params, u32 B, u32 limb0) {
+__global__ void __launch_bounds__(256, 2)
+k_col_inv(const u64* in, u64* out, const Tables tabs, u32 S, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC>;
-    constexpr u32 logN = 24 - LOGC;
     __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
     const u32 tid = threadIdx.x;
-    const u32 p = blockIdx.x >> (12 - LOGC), tile = blockIdx.x & ((1u << (12 - LOGC)) - 1u);
-    const u64 base = ((u64)p << logN) + ((u64)tile << LOGC);
-    const u32 limb = limb0 + p / B;
-    const LimbParams P = params[limb];
-    const ulonglong2* tw = twi + ((size_t)limb << logN);
+    const ColId id = col_id<LOGC>(S, B, limb0);
+    const LimbParams* __restrict__ Pg = tabs.params + id.limb;
+    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << (S + 12 - LOGC));
     u64 r[kElems];
     if constexpr (Geo::TWO) {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(base, elem_index<4>(tid, i))];
-        inv_round<3, Geo::LO4, false>(r, tw, 16u + (tid >> 4), P);
+        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<4>(tid, i), S)];
+        inv_round<3, Geo::LO4, false>(r, TwStd{tw, 16u + (tid >> 4)}, q2, nq, Pg);
         sm_store<4>(sm, tid, r);
         __syncthreads();
         sm_load<8>(sm, tid, r);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(base, elem_index<8>(tid, i))];
+        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<8>(tid, i), S)];
     }
-    inv_round<3, Geo::LO8, true>(r, tw, 1u, P);
+    inv_round<3, Geo::LO8, true>(r, TwStd{tw, 1u}, q2, nq, Pg);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) out[Geo::addr(base, elem_index<8>(tid, i))] = r[i];
+    for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<8>(tid, i), S)] = r[i];
 }
 
 // ------------------------------------------------------------------------------------------------
 // host-side dispatch
 // ------------------------------------------------------------------------------------------------
 #define GFHE_ROW_CASES(X) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12)
-#define GFHE_COL_CASES(X) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11)
+#define GFHE_COL_CASES(X) X(4) X(5) X(6) X(7)
 
-static inline unsigned slabs_of(const Plan& pl, u32 nl, u32 B) {
-    const u32 logS = pl.logN < (u32)kMaxLogSlab ? pl.logN : (u32)kMaxLogSlab;
-    return (unsigned)(((u64)nl * B) << (pl.logN - logS));
+static inline Tables fwd_tables(const Plan& pl) { return Tables{pl.d_fwd, pl.d_fwd_t0, pl.d_params}; }
+static inline Tables inv_tables(const Plan& pl) { return Tables{pl.d_inv, pl.d_inv_t0, pl.d_params}; }
+
+// Stage split of a two-pass transform: S low (row) stages, log2 N - S <= 8 high (column) stages.
+static inline u32 row_stages(u32 logN) { return logN <= 16 ? 8u : 12u; }
+
+static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
+    const u32 logT = pl.logN < (u32)kMaxLogSlab ? pl.logN : (u32)kMaxLogSlab;
+    return (unsigned)(((u64)nl * B) << (pl.logN - logT));
+}
+
+template <int LOGS>
+static void launch_row_fwd12(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
+    ProfScope ps(pl, K_ROW_FWD, st);
+    k_row_fwd<LOGS, 12><<<nt, 256, 0, st>>>(in, out, fwd_tables(pl), pl.logN, B, limb0);
+}
+template <int LOGS>
+static void launch_row_inv12(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
+    ProfScope ps(pl, K_ROW_INV, st);
+    k_row_inv<LOGS, 12, false><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0);
 }
 
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const unsigned nslab = slabs_of(pl, nl, B);
+    const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<LS><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0); } break;
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<LS, LS><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, fwd_tables(pl), pl.logN, B, limb0); } break;
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
-    } else {
-        switch (24 - (int)pl.logN) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nslab, 1), 256, 0, st>>>(in, out, nullptr, nullptr, pl.d_fwd, pl.d_params, B, limb0); } break;
-            GFHE_COL_CASES(X)
-#undef X
-            default: return cudaErrorInvalidValue;
-        }
-        { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<12><<<nslab, 256, 0, st>>>(out, out, pl.d_fwd, pl.d_params, pl.logN, B, limb0); }
+        return cudaGetLastError();
     }
+    const u32 S = row_stages(pl.logN);
+    switch (12 - (int)(pl.logN - S)) {
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nt, 1), 256, 0, st>>>(in, out, nullptr, nullptr, fwd_tables(pl), S, B, limb0); } break;
+        GFHE_COL_CASES(X)
+#undef X
+        default: return cudaErrorInvalidValue;
+    }
+    if (S == 8) launch_row_fwd12<8>(pl, limb0, out, out, B, nt, st);
+    else launch_row_fwd12<12>(pl, limb0, out, out, B, nt, st);
     return cudaGetLastError();
 }
 
 cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const unsigned nslab = slabs_of(pl, nl, B);
+    const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<LS, true><<<nslab, RowGeo<LS>::NT, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0); } break;
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<LS, LS, true><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0); } break;
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
-    } else {
-        { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<12, false><<<nslab, 256, 0, st>>>(in, out, pl.d_inv, pl.d_params, pl.logN, B, limb0); }
-        switch (24 - (int)pl.logN) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nslab, 256, 0, st>>>(out, out, pl.d_inv, pl.d_params, B, limb0); } break;
-            GFHE_COL_CASES(X)
+        return cudaGetLastError();
+    }
+    const u32 S = row_stages(pl.logN);
+    if (S == 8) launch_row_inv12<8>(pl, limb0, in, out, B, nt, st);
+    else launch_row_inv12<12>(pl, limb0, in, out, B, nt, st);
+    switch (12 - (int)(pl.logN - S)) {
+#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nt, 256, 0, st>>>(out, out, inv_tables(pl), S, B, limb0); } break;
+        GFHE_COL_CASES(X)
 #undef X
-            default: return cudaErrorInvalidValue;
-        }
+        default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
 }
 
-template <int LOGS, bool WHOLE>
-static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nslab,
+template <int LOGS, int LOGT, bool WHOLE>
+static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
-    const size_t smem = (size_t)2 * sizeof(u64) << LOGS;
+    const size_t smem = (size_t)2 * sizeof(u64) << LOGT;
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<LOGS, WHOLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<LOGS, LOGT, WHOLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured[dev] = true;
     }
-    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<LOGS, WHOLE><<<nslab, RowGeo<LOGS>::NT, smem, st>>>(a, b, c, pl.d_fwd, pl.d_inv, pl.d_params, pl.logN, B, limb0); }
+    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<LOGS, LOGT, WHOLE><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
     return cudaGetLastError();
 }
 
@@ -299,27 +342,30 @@ size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
 }
 
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
-    const unsigned nslab = slabs_of(pl, nl, B);
+    const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: return launch_row_polymul<LS, true>(pl, limb0, a, b, c, B, nslab, st);
+#define X(LS) case LS: return launch_row_polymul<LS, LS, true>(pl, limb0, a, b, c, B, nt, st);
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
     }
     if (!ws) return cudaErrorInvalidValue;
+    const u32 S = row_stages(pl.logN);
+    const int LC = 12 - (int)(pl.logN - S);
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
-    switch (24 - (int)pl.logN) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nslab, 2), 256, 0, st>>>(a, c, b, ws, pl.d_fwd, pl.d_params, B, limb0); } break;
+    switch (LC) {
+#define X(LCC) case LCC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LCC><<<dim3(nt, 2), 256, 0, st>>>(a, c, b, ws, fwd_tables(pl), S, B, limb0); } break;
         GFHE_COL_CASES(X)
 #undef X
         default: return cudaErrorInvalidValue;
     }
-    cudaError_t e = launch_row_polymul<12, false>(pl, limb0, c, ws, c, B, nslab, st);
+    cudaError_t e = S == 8 ? launch_row_polymul<8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
+                           : launch_row_polymul<12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
     if (e != cudaSuccess) return e;
-    switch (24 - (int)pl.logN) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nslab, 256, 0, st>>>(c, c, pl.d_inv, pl.d_params, B, limb0); } break;
+    switch (LC) {
+#define X(LCC) case LCC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LCC><<<nt, 256, 0, st>>>(c, c, inv_tables(pl), S, B, limb0); } break;
         GFHE_COL_CASES(X)
 #undef X
         default: return cudaErrorInvalidValue;

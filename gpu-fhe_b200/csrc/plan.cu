@@ -67,6 +67,19 @@ static void fill_tables(ulonglong2* fwd, ulonglong2* inv, u64 q, u32 logN, u64 p
     }
 }
 
+// t0[j][t] = std[(N >> (b+1)) + t * 2^(3-b) + hi],  j = (2^(3-b) - 1) + hi,  b = 0..3  (ntt_core.cuh, TwT0)
+static void fill_t0(ulonglong2* t0, const ulonglong2* std_tab, u32 logN) {
+    const u64 N = 1ull << logN, T = N >> 4;
+    for (u32 b = 0; b < 4; ++b) {
+        const u32 cnt = 1u << (3 - b);
+        for (u32 hi = 0; hi < cnt; ++hi) {
+            ulonglong2* row = t0 + (size_t)((cnt - 1) + hi) * T;
+            const ulonglong2* src = std_tab + (N >> (b + 1)) + hi;
+            for (u64 t = 0; t < T; ++t) row[t] = src[t * cnt];
+        }
+    }
+}
+
 int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi) {
     if (!out || !moduli || L == 0) return -1;
     if (logN != 0 && (logN < 4 || logN > 20 || !psi)) return -2;
@@ -91,9 +104,11 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
 
     if (logN) {
         const size_t N = (size_t)1 << logN, bytes = sizeof(ulonglong2) * N * L;
-        ulonglong2 *hf = nullptr, *hi = nullptr;
+        const size_t n0 = 15 * (N >> 4), bytes0 = sizeof(ulonglong2) * n0 * L;
+        ulonglong2 *hf = nullptr, *hi = nullptr, *hf0 = nullptr, *hi0 = nullptr;
         hf = (ulonglong2*)std::malloc(bytes); hi = (ulonglong2*)std::malloc(bytes);
-        if (!hf || !hi) { std::free(hf); std::free(hi); plan_destroy(pl); return -6; }
+        hf0 = (ulonglong2*)std::malloc(bytes0); hi0 = (ulonglong2*)std::malloc(bytes0);
+        if (!hf || !hi || !hf0 || !hi0) { std::free(hf); std::free(hi); std::free(hf0); std::free(hi0); plan_destroy(pl); return -6; }
         unsigned nthr = std::thread::hardware_concurrency();
         if (nthr == 0) nthr = 1;
         if (nthr > L) nthr = L;
@@ -101,14 +116,22 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
         std::vector<std::thread> pool;
         for (unsigned t = 0; t < nthr; ++t)
             pool.emplace_back([=]() {
-                for (u32 l = t; l < L; l += nthr) fill_tables(hf + l * N, hi + l * N, moduli[l], logN, psi[l]);
+                for (u32 l = t; l < L; l += nthr) {
+                    fill_tables(hf + l * N, hi + l * N, moduli[l], logN, psi[l]);
+                    fill_t0(hf0 + l * n0, hf + l * N, logN);
+                    fill_t0(hi0 + l * n0, hi + l * N, logN);
+                }
             });
         for (auto& th : pool) th.join();
         e = cudaMalloc(&pl->d_fwd, bytes);
         if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv, bytes);
         if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd, hf, bytes, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv, hi, bytes, cudaMemcpyHostToDevice);
-        std::free(hf); std::free(hi);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_fwd_t0, bytes0);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv_t0, bytes0);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd_t0, hf0, bytes0, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv_t0, hi0, bytes0, cudaMemcpyHostToDevice);
+        std::free(hf); std::free(hi); std::free(hf0); std::free(hi0);
         if (e != cudaSuccess) { plan_destroy(pl); return (int)e; }
     }
     *out = pl;
@@ -129,6 +152,8 @@ int plan_destroy(Plan* p) {
     if (p->d_params) cudaFree(p->d_params);
     if (p->d_fwd) cudaFree(p->d_fwd);
     if (p->d_inv) cudaFree(p->d_inv);
+    if (p->d_fwd_t0) cudaFree(p->d_fwd_t0);
+    if (p->d_inv_t0) cudaFree(p->d_inv_t0);
     delete p;
     return 0;
 }

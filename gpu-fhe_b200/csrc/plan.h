@@ -28,6 +28,8 @@ struct Plan {
     LimbParams* d_params = nullptr;    // [L]
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
+    ulonglong2* d_fwd_t0 = nullptr;    // [L][15][N/16] transposed copy of d_fwd for the window at bit 0
+    ulonglong2* d_inv_t0 = nullptr;    // [L][15][N/16] same for d_inv (ntt_core.cuh, TwT0)
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
     Profiler* prof = nullptr;
 };

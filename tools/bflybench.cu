@@ -1,0 +1,198 @@
+// Butterfly-variant microbenchmark for sm_100a: issue-clocks per 60-bit butterfly for candidate
+// arithmetic (exact vs approximate high product, exact vs high-word conditional subtraction).
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o bflybench tools/bflybench.cu && ./bflybench
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../gpu-fhe_b200/csrc/modarith.cuh"
+using namespace gfhe;
+
+constexpr int ITERS = 512, CH = 8;
+
+// approximate-high Shoup: h' in {h-2..h}, result in [0,4q) for any 64-bit x (5 WIDE + 4 IMAD)
+__device__ __forceinline__ u64 shoup_a(u64 x, u64 w, u64 ws, u64 nq) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,wl,wh,pl,ph,nl,nh,h0,h1,top,lo,d;\n\t"
+        ".reg .u64 t1,t2,h,acc;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {wl,wh}, %2;\n\t"
+        "mov.b64 {pl,ph}, %3;\n\t"
+        "mov.b64 {nl,nh}, %4;\n\t"
+        "mul.wide.u32 t1, xl, ph;\n\t"
+        "mov.b64 {d,h0}, t1;\n\t"
+        "cvt.u64.u32 t1, h0;\n\t"
+        "mad.wide.u32 t2, xh, pl, t1;\n\t"
+        "mov.b64 {d,h0}, t2;\n\t"
+        "cvt.u64.u32 t2, h0;\n\t"
+        "mad.wide.u32 h, xh, ph, t2;\n\t"
+        "mov.b64 {h0,h1}, h;\n\t"
+        "mul.wide.u32 acc, xl, wl;\n\t"
+        "mad.wide.u32 acc, h0, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, xl, wh, top;\n\t"
+        "mad.lo.u32 top, xh, wl, top;\n\t"
+        "mad.lo.u32 top, h0, nh, top;\n\t"
+        "mad.lo.u32 top, h1, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n" : "=l"(r) : "l"(x), "l"(w), "l"(ws), "l"(nq));
+    return r;
+}
+// high-word conditional subtraction: subtracts c when hi32(x) > hi32(c); result < max(c + 2^32, x - c)
+__device__ __forceinline__ u64 csub_hi(u64 x, u64 c) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,cl,ch;\n\t"
+        ".reg .pred p;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {cl,ch}, %2;\n\t"
+        "setp.gt.u32 p, xh, ch;\n\t"
+        "@p sub.cc.u32 xl, xl, cl;\n\t"
+        "@p subc.u32 xh, xh, ch;\n\t"
+        "mov.b64 %0, {xl,xh};\n\t"
+        "}\n" : "=l"(r) : "l"(x), "l"(c));
+    return r;
+}
+
+// FP64-assisted product: x*w mod q from the split x = xh*2^32 + xl with w0 = w, w1 = w*2^32 mod q and
+// the quotient of each half estimated on the FP64 pipe (r0 = w0/q, r1 = w1/q as doubles).
+// Returns r + K (mod 2^64), r in [-1.01q, 1.01q], K = 0x43300000 * nql * 2^32 a per-limb constant.
+__device__ __forceinline__ u64 dfmul(u64 x, u64 w0, u64 w1, double r0, double r1, u64 nq) {
+    const u32 xl = (u32)x, xh = (u32)(x >> 32);
+    const double ul = __hiloint2double(0x43300000, (int)xl) - 4503599627370496.0;
+    const double uh = __hiloint2double(0x43300000, (int)xh) - 4503599627370496.0;
+    const double R = fma(ul, r0, fma(uh, r1, 4503599627370496.0));
+    const u32 hlo = (u32)__double2loint(R), hhi = (u32)__double2hiint(R);
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 al,ah,bl,bh,nl,nh,top,lo;\n\t"
+        ".reg .u64 acc;\n\t"
+        "mov.b64 {al,ah}, %3;\n\t"
+        "mov.b64 {bl,bh}, %4;\n\t"
+        "mov.b64 {nl,nh}, %5;\n\t"
+        "mul.wide.u32 acc, %1, al;\n\t"
+        "mad.wide.u32 acc, %2, bl, acc;\n\t"
+        "mad.wide.u32 acc, %6, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, %1, ah, top;\n\t"
+        "mad.lo.u32 top, %2, bh, top;\n\t"
+        "mad.lo.u32 top, %6, nh, top;\n\t"
+        "mad.lo.u32 top, %7, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n" : "=l"(r) : "r"(xl), "r"(xh), "l"(w0), "l"(w1), "l"(nq), "r"(hlo), "r"(hhi));
+    return r;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u64 w, u64 ws) {
+    u64 X[CH], Y[CH];
+    const u64 q2 = 2 * q, q4 = 4 * q, nq = 0 - q;
+    const double r0 = (double)w / (double)q, r1 = (double)ws / 18446744073709551616.0;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) { X[i] = (threadIdx.x * 1315423911ull + i) % q; Y[i] = (threadIdx.x * 2654435761ull + 7 * i) % q; }
+    __syncthreads();
+    u64 g0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+            if (MODE == 0) {          // current: exact shoup, exact csub, [0,4q)
+                const u64 x = csub(X[i], q2), t = shoup_mul(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q2;
+            } else if (MODE == 1) {   // approx shoup, exact csub, [0,8q)
+                const u64 x = csub(X[i], q4), t = shoup_a(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 2) {   // approx shoup, high-word csub
+                const u64 x = csub_hi(X[i], q4), t = shoup_a(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 3) {   // approx shoup, no csub (timing floor only; values wrap)
+                const u64 x = X[i], t = shoup_a(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 4) {   // inverse, current
+                const u64 u = X[i], v = Y[i];
+                X[i] = csub(u + v, q2); Y[i] = shoup_mul(u - v + q2, w, ws, nq);
+            } else if (MODE == 5) {   // inverse, approx shoup + exact csub
+                const u64 u = X[i], v = Y[i];
+                X[i] = csub(u + v, q4); Y[i] = shoup_a(u - v + q4, w, ws, nq);
+            } else if (MODE == 6) {   // inverse, approx shoup + high-word csub
+                const u64 u = X[i], v = Y[i];
+                X[i] = csub_hi(u + v, q4); Y[i] = shoup_a(u - v + q4, w, ws, nq);
+            } else if (MODE == 9) {   // FP64-assisted, no csub
+                const u64 t = dfmul(Y[i], w, ws, r0, r1, nq);
+                const u64 x = X[i];
+                X[i] = x + t + q2; Y[i] = x - t + q4;
+            } else if (MODE == 10) {  // FP64-assisted, exact csub on every second butterfly (one per two stages)
+                const u64 t = dfmul(Y[i], w, ws, r0, r1, nq);
+                const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i];
+                X[i] = x + t + q2; Y[i] = x - t + q4;
+            } else if (MODE == 11) {  // FP64-assisted, exact csub every butterfly
+                const u64 t = dfmul(Y[i], w, ws, r0, r1, nq);
+                const u64 x = csub(X[i], q4);
+                X[i] = x + t + q2; Y[i] = x - t + q4;
+            } else if (MODE == 12) {  // approx shoup, csub on every second butterfly
+                const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i], t = shoup_a(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 7) {   // shoup_a alone
+                Y[i] = shoup_a(Y[i] + X[i], w, ws, nq);
+            } else {                  // barrett product (pointwise)
+                Y[i] = barrett_mul(csub(Y[i], q), csub(X[i], q), q, ws, 59);
+            }
+        }
+    }
+    long long t1 = clock64();
+    u64 g1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+    u64 acc = 0;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) acc += X[i] ^ Y[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+    if (threadIdx.x == 0) { cyc[blockIdx.x] = t1 - t0; cyc[gridDim.x + blockIdx.x] = (long long)(g1 - g0); }
+}
+
+template <int MODE>
+static void run(const char* name, int sms, int threads = 512) {
+    const u64 q = 1152921504606584833ull, w = 987813353222176621ull;
+    const u64 ws = (u64)(((unsigned __int128)w << 64) / q);
+    u64* out; long long* cyc;
+    const int blocks = sms * 2 * 8;   // 8 full waves of 2 co-resident 512-thread CTAs per SM
+    cudaMalloc(&out, sizeof(u64) * blocks * 512); cudaMalloc(&cyc, sizeof(long long) * blocks * 2);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    kb<MODE><<<blocks, threads>>>(out, cyc, q, w, ws);
+    cudaEventRecord(e0);
+    kb<MODE><<<blocks, threads>>>(out, cyc, q, w, ws);
+    cudaEventRecord(e1);
+    cudaDeviceSynchronize();
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    long long* h = new long long[blocks * 2];
+    cudaMemcpy(h, cyc, sizeof(long long) * blocks * 2, cudaMemcpyDeviceToHost);
+    double mean = 0, ns = 0; for (int i = 0; i < blocks; ++i) { mean += h[i]; ns += h[blocks + i]; } mean /= blocks; ns /= blocks;
+    const double mhz = mean / ns * 1e3;
+    const double nb = (double)blocks * threads * ITERS * CH;          // thread-butterflies
+    const double per_s = nb / (ms * 1e-3);
+    // whole-kernel figure: warp-butterflies per SMSP = nb/32/(sms*4); clocks at 1.965 GHz
+    const double clk_ev = (ms * 1e-3 * 1.965e9) / (nb / 32 / (sms * 4.0));
+    printf("%-42s %6.2f Tbfly/s  %6.2f clk/warp-bfly/SMSP (events @1.965GHz)  %6.2f (clock64, 8 warps/SMSP)  SM clock %4.0f MHz (clock64/globaltimer)  err=%s\n", name,
+           per_s * 1e-12, clk_ev, mean / (8.0 * ITERS * CH), mhz, cudaGetErrorString(cudaGetLastError()));
+    delete[] h; cudaFree(out); cudaFree(cyc);
+}
+
+int main() {
+    int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    run<0>("fwd  exact shoup + exact csub (current)", sms);
+    run<0>("  same, 4 warps/SMSP (2 x 256 thr/SM)", sms, 256);
+    run<0>("  same, 2 warps/SMSP (2 x 128 thr/SM)", sms, 128);
+    run<12>("fwd approx shoup csub/2, 4 warps/SMSP", sms, 256);
+    run<1>("fwd  approx shoup + exact csub", sms);
+    run<2>("fwd  approx shoup + high-word csub", sms);
+    run<3>("fwd  approx shoup, no csub (floor)", sms);
+    run<4>("inv  exact shoup + exact csub (current)", sms);
+    run<5>("inv  approx shoup + exact csub", sms);
+    run<6>("inv  approx shoup + high-word csub", sms);
+    run<9>("fwd  FP64-assisted, no csub", sms);
+    run<10>("fwd  FP64-assisted, csub every 2nd", sms);
+    run<11>("fwd  FP64-assisted, csub every bfly", sms);
+    run<12>("fwd  approx shoup, csub every 2nd", sms);
+    run<7>("shoup_a alone (+1 add)", sms);
+    run<8>("barrett_mul (+2 csub)", sms);
+    return 0;
+}

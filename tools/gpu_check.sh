@@ -1,10 +1,14 @@
 #!/bin/bash
 # One gpurun call: parity tests, smoke, bench, then (only after the plain runs exited 0) the ncu
 # launch list of the same bench command and one --set full capture of the dominant kernels.
-# Outputs land in gpurun_out/.   usage: tools/gpu_check.sh [notests] [noncu]
+# Outputs land in gpurun_out/.   usage: tools/gpu_check.sh [notests] [noncu] [micro]
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw,memory.total --format=csv > gpurun_out/smi.csv 2>&1
 nproc > gpurun_out/nproc.txt
+if [[ " $* " == *" micro "* ]]; then
+  for b in pipebench bflybench; do [ -x tools/$b ] && timeout 120 tools/$b > gpurun_out/$b.txt 2>&1; done
+  cat gpurun_out/bflybench.txt
+fi
 if [[ " $* " != *" notests "* ]]; then
   timeout 1200 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
   tail -15 gpurun_out/pytest_gpu.log

@@ -6,6 +6,7 @@
 // supplies the butterfly arithmetic the reference's NTT/iNTT stubs (arithmetic.py:15-19)
 // never had.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 
 namespace gfhe {
@@ -15,18 +16,25 @@ typedef unsigned int u32;
 
 // Per-limb constants, generated on the host (plan.cu) and resident in HBM.
 struct __align__(16) LimbParams {
+    u64 q2;         // 2q                      } one 16-byte load (ntt_kernels.inl, limb_consts)
+    u64 nq;         // -q mod 2^64             }
     u64 q;          // modulus, odd, < 2^62
-    u64 q2;         // 2q
-    u64 nq;         // -q mod 2^64
     u64 bar_mu;     // floor(2^(k+63) / q), k = bit length of q  (single-mulhi Barrett)
-    u64 ninv;       // N^-1 mod q
-    u64 ninv_s;     // Shoup companion of ninv
+    u64 ninv;       // N^-1 mod q              } 16-byte aligned pair
+    u64 ninv_s;     // Shoup companion of ninv }
     u64 w1ninv;     // psi^-brv(1) * N^-1 mod q  (last inverse stage, N^-1 folded in)
     u64 w1ninv_s;
     u64 bar64;      // floor(2^64 / q): one-word Barrett for reducing arbitrary 64-bit inputs
     u32 bar_shift;  // k - 1
-    u32 pad;
+    u32 kshift;     // k - 17 (kred: y = x >> kshift fits 32 bits for x < 16q); valid when k >= 20
+    u64 kmu;        // floor(2^(32 + kshift) / q) <= 2^16
+    u64 pad;
 };
+static_assert(sizeof(LimbParams) == 96, "LimbParams layout");
+
+// Layout of the warp-tiled twiddle copy (plan.cu fills it, ntt_core.cuh TwT0 reads it).
+constexpr u32 kT0Block = 15 * 32;   // entries per warp-tile
+__host__ __device__ constexpr size_t t0_entries(size_t N) { return (((N >> 4) + 31) >> 5) * kT0Block; }
 
 // x*w mod q up to a multiple of q: returns x*w - floor(x*ws/2^64)*q in [0, 2q) for ANY 64-bit x,
 // given ws = floor(w*2^64/q), w < q, and nq = -q mod 2^64.
@@ -102,5 +110,68 @@ __device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, u64 q, u64 mu, u32 s) {
 __device__ __forceinline__ u64 barrett_mul(u64 a, u64 b, const LimbParams& P) {
     return barrett_mul(a, b, P.q, P.bar_mu, P.bar_shift);
 }
+
+// ---- lazy arithmetic for moduli with four spare bits (2^19 <= q < 2^60) --------------------------
+// Approximate-high Shoup product: the quotient estimate xh*ph + hi32(xl*ph) + hi32(xh*pl) drops the
+// lo*lo partial product and the low halves of the cross products, so it is the exact one minus 0, 1
+// or 2 and the result is
+// x*w - h'*q in [0, 4q) for ANY 64-bit x.  5 IMAD.WIDE + 4 IMAD (the exact form needs two IMAD.HI,
+// the slowest integer multiply on sm_100a, see tools/pipebench.cu).
+__device__ __forceinline__ u64 shoup_a(u64 x, u64 w, u64 ws, u64 nq) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,wl,wh,pl,ph,nl,nh,h0,h1,top,lo,d;\n\t"
+        ".reg .u64 t1,t2,h,acc;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {wl,wh}, %2;\n\t"
+        "mov.b64 {pl,ph}, %3;\n\t"
+        "mov.b64 {nl,nh}, %4;\n\t"
+        "mul.wide.u32 t1, xl, ph;\n\t"
+        "mul.wide.u32 t2, xh, pl;\n\t"
+        "mov.b64 {d,h0}, t1;\n\t"
+        "mov.b64 {d,h1}, t2;\n\t"
+        "add.cc.u32 h0, h0, h1;\n\t"
+        "addc.u32 h1, 0, 0;\n\t"
+        "mov.b64 t1, {h0,h1};\n\t"
+        "mad.wide.u32 h, xh, ph, t1;\n\t"
+        "mov.b64 {h0,h1}, h;\n\t"
+        "mul.wide.u32 acc, xl, wl;\n\t"
+        "mad.wide.u32 acc, h0, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, xl, wh, top;\n\t"
+        "mad.lo.u32 top, xh, wl, top;\n\t"
+        "mad.lo.u32 top, h0, nh, top;\n\t"
+        "mad.lo.u32 top, h1, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n"
+        : "=l"(r)
+        : "l"(x), "l"(w), "l"(ws), "l"(nq));
+    return r;
+}
+
+// x mod q up to one q, for x < 16q: k' = floor((x >> kshift) * kmu / 2^32) is floor(x/q) or one less
+// (x >> kshift < 2^21, kmu <= 2^16), so x - k'*q is in [0, 2q).  SHF + IMAD.WIDE(.hi) + IMAD.WIDE + IMAD.
+__device__ __forceinline__ u64 kred(u64 x, u32 kshift, u32 kmu, u64 nq) {
+    const u32 y = (u32)(x >> kshift);
+    const u32 k = (u32)(((u64)y * kmu) >> 32);
+    return x + (u64)k * nq;
+}
+
+// Arithmetic policies of the butterfly code (ntt_core.cuh).
+//   Harvey : exact Shoup, any q < 2^62.  forward residues in [0,4q), inverse in [0,2q).
+//   Lazy60 : approximate Shoup, 2^19 <= q < 2^60.  forward residues in [0,16q) with one conditional
+//            subtraction of 8q every second stage, inverse residues in [0,8q).
+struct Harvey {
+    static constexpr bool kLazy = false;
+    static constexpr int kFwdC = 2;   // forward offset/csub constant = kFwdC * q
+    static constexpr int kInvC = 2;
+    __device__ static __forceinline__ u64 mul(u64 x, u64 w, u64 ws, u64 nq) { return shoup_mul(x, w, ws, nq); }
+};
+struct Lazy60 {
+    static constexpr bool kLazy = true;
+    static constexpr int kFwdC = 4;   // T < 4q
+    static constexpr int kInvC = 8;
+    __device__ static __forceinline__ u64 mul(u64 x, u64 w, u64 ws, u64 nq) { return shoup_a(x, w, ws, nq); }
+};
 
 }  // namespace gfhe

@@ -4,9 +4,10 @@
 // registers and runs up to four radix-2 stages ("a round") on them without touching memory;
 // between rounds the slab is re-distributed through XOR-swizzled shared memory.
 //
-//   forward : Cooley-Tukey, natural in -> bit-reversed out, lazy residues in [0, 4q)
-//   inverse : Gentleman-Sande, bit-reversed in -> natural out, lazy residues in [0, 2q),
+//   forward : Cooley-Tukey, natural in -> bit-reversed out, lazy residues in [0, 4q) (Harvey) / [0,16q) (Lazy60)
+//   inverse : Gentleman-Sande, bit-reversed in -> natural out, lazy residues in [0, 2q) / [0, 8q),
 //             N^-1 folded into the twiddles of the last stage
+// The arithmetic policy A (modarith.cuh) is chosen per plan: Lazy60 when every modulus has four spare bits.
 //
 // The bit reversal is never materialised: it is absorbed by running the stages top bit first
 // (forward) / bottom bit first (inverse) with bit-reversed twiddle tables.
@@ -48,58 +49,71 @@ __device__ __forceinline__ ulonglong2 ldg_tw(const ulonglong2* p) {
 //        the window share v, so a warp request touches 1-2 lines.
 //  T0  : the window at bit 0 (each thread owns 16 contiguous residues and 15 private twiddles).  Reading
 //        them from the standard table costs 32 lines per warp request; the plan therefore keeps a second,
-//        transposed copy  t0[j][t],  j = (2^(3-b) - 1) + hi in [0,15),  t = (residue index) / 16,  so the
-//        lanes of a warp read consecutive 16-byte entries.
+//        warp-tiled copy  t0[t / 32][j][t % 32],  j = (2^(3-b) - 1) + hi in [0,15),  t = (residue index) / 16,
+//        so the lanes of a warp read consecutive 16-byte entries and the 15 loads of a thread are ONE pointer
+//        plus immediate offsets j * 512 bytes (no per-load address arithmetic, nothing to hoist and spill).
 struct TwStd {
     const ulonglong2* __restrict__ tw; u32 v;
     __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(tw + ((v << (3 - b)) + hi)); }
 };
 struct TwT0 {
-    const ulonglong2* __restrict__ p; u32 stride;     // p = t0 + t, stride = N/16
-    __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(p + (size_t)(((1 << (3 - b)) - 1) + hi) * stride); }
+    const ulonglong2* __restrict__ p;                  // t0 + (t / 32) * kT0Block + t % 32
+    __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(p + ((((1 << (3 - b)) - 1) + hi) << 5)); }
 };
 
 // ---- one round of forward (CT) stages on local bits B_HI..B_LO --------------------------------
 // v = (twiddle-table index of the thread's group at the round's top stage); the table index of
 // local bit b, sub-group hi is (v << (3-b)) + hi  (see DESIGN.md "twiddle indexing").
-template <int B_HI, int B_LO, class TW>
-__device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 q2, u64 nq) {
+// C = A::kFwdC * q.  Harvey: residues in [0,4q), X is brought under 2q every stage.  Lazy60: residues
+// in [0,16q); the product is < 4q, so X grows by 4q per stage and is brought under 8q at the first
+// and third stage of a round (every round therefore maps [0,16q) to [0,16q)).
+template <class A, int B_HI, int B_LO, class TW>
+__device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 C, u64 nq) {
 #pragma unroll
     for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
         const int b = B_HI - sidx;
+        const bool reduce_x = !A::kLazy || (sidx & 1) == 0;
 #pragma unroll
         for (int hi = 0; hi < (8 >> b); ++hi) {
             const ulonglong2 t = tw.get(b, hi);
 #pragma unroll
             for (int lo = 0; lo < (1 << b); ++lo) {
                 const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
-                const u64 X = csub(r[ix], q2);                       // [0,4q) -> [0,2q)
-                const u64 T = shoup_mul(r[iy], t.x, t.y, nq);       // [0,2q)
-                r[ix] = X + T;                                        // [0,4q)
-                r[iy] = X - T + q2;                                   // [0,4q)
+                const u64 X = reduce_x ? csub(r[ix], A::kLazy ? 2 * C : C) : r[ix];
+                const u64 T = A::mul(r[iy], t.x, t.y, nq);
+                r[ix] = X + T;
+                r[iy] = X - T + C;
             }
         }
     }
 }
 
+// Full reduction of a forward residue to [0, q).
+template <class A>
+__device__ __forceinline__ u64 fwd_final(u64 x, u64 q, u64 nq, u32 kshift, u32 kmu) {
+    if constexpr (A::kLazy) return csub(kred(x, kshift, kmu, nq), q);   // [0,16q) -> [0,2q) -> [0,q)
+    else return csub(csub(x, 2 * q), q);                                // [0,4q)
+}
+
 // ---- one round of inverse (GS) stages on local bits B_LO..B_HI --------------------------------
+// C = A::kInvC * q: residues stay in [0, C) (Harvey 2q, Lazy60 8q).
 // LAST: local bit B_HI is the final stage of the whole transform; it multiplies by N^-1
-// (folded: U' = (U+V)*N^-1, V' = (U-V)*psi^-brv(1)*N^-1) and fully reduces to [0, q).
-template <int B_HI, int B_LO, bool LAST, class TW>
-__device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 q2, u64 nq, const LimbParams* __restrict__ Pg) {
+// (folded: U' = (U+V)*N^-1, V' = (U-V)*psi^-brv(1)*N^-1) with the exact product and fully reduces to [0, q).
+template <class A, int B_HI, int B_LO, bool LAST, class TW>
+__device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 C, u64 nq, const LimbParams* __restrict__ Pg) {
 #pragma unroll
     for (int b = B_LO; b <= B_HI; ++b) {
         if (LAST && b == B_HI) {
             // per-limb constants of the final stage are fetched here, not held in registers all along
             const ulonglong2 cn = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->ninv));
             const ulonglong2 cw = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->w1ninv));
-            const u64 q = q2 >> 1;
+            const u64 q = 0 - nq;
 #pragma unroll
             for (int lo = 0; lo < (1 << b); ++lo) {                  // B_HI == 3 here: one group
                 const int ix = lo, iy = ix + (1 << b);
                 const u64 U = r[ix], V = r[iy];
                 r[ix] = csub(shoup_mul(U + V, cn.x, cn.y, nq), q);
-                r[iy] = csub(shoup_mul(U - V + q2, cw.x, cw.y, nq), q);
+                r[iy] = csub(shoup_mul(U - V + C, cw.x, cw.y, nq), q);
             }
         } else {
 #pragma unroll
@@ -109,8 +123,8 @@ __device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 q2,
                 for (int lo = 0; lo < (1 << b); ++lo) {
                     const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
                     const u64 U = r[ix], V = r[iy];
-                    r[ix] = csub(U + V, q2);                          // [0,2q)
-                    r[iy] = shoup_mul(U - V + q2, t.x, t.y, nq);      // [0,2q)
+                    r[ix] = csub(U + V, C);                           // [0,C)
+                    r[iy] = A::mul(U - V + C, t.x, t.y, nq);          // [0,2q) or [0,4q)
                 }
             }
         }
@@ -154,13 +168,16 @@ struct Sched {
 // Per-limb twiddle tables (already offset to the limb) and the ring degree.
 struct TwTab {
     const ulonglong2* __restrict__ tw;   // [N]       standard bit-reversed table
-    const ulonglong2* __restrict__ t0;   // [15][N/16] transposed copy for the window at bit 0
+    const ulonglong2* __restrict__ t0;   // [N/512][15][32] warp-tiled copy for the window at bit 0
     u32 N;
 };
 // Twiddle source of the round whose window sits at slab bit P0; off = offset of the slab in its polynomial.
 template <int P0>
 __device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
-    if constexpr (P0 == 0) return TwT0{T.t0 + ((off >> 4) + tid), T.N >> 4};
+    if constexpr (P0 == 0) {
+        const u32 t = (off >> 4) + tid;
+        return TwT0{T.t0 + ((t >> 5) * kT0Block + (t & 31u))};
+    }
     else return TwStd{T.tw, ((T.N + off) >> (P0 + 4)) + (tid >> P0)};
 }
 
@@ -168,19 +185,19 @@ __device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
 // On entry r[] holds the layout of round 0 (window at bit p0(0)); on exit the layout of the last round
 // (window at bit 0: 16 contiguous residues per thread).  The slab may be a tile of several independent
 // 2^LOGS-point sub-transforms (tid then spans more than 2^(LOGS-4) threads): nothing here depends on it.
-template <int LOGS>
-__device__ __forceinline__ void slab_fwd(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 q2, u64 nq) {
+template <class A, int LOGS>
+__device__ __forceinline__ void slab_fwd(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 C, u64 nq) {
     using S = Sched<LOGS>;
     {
         constexpr int P0 = S::p0(0);
-        fwd_round<S::top(0) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), q2, nq);
+        fwd_round<A, S::top(0) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
     }
     if constexpr (S::NR > 1) {
         constexpr int PP = S::p0(0), P0 = S::p0(1);
         sm_store<PP>(sm, tid, r);
         __syncthreads();
         sm_load<P0>(sm, tid, r);
-        fwd_round<S::top(1) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), q2, nq);
+        fwd_round<A, S::top(1) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
     }
     if constexpr (S::NR > 2) {
         constexpr int PP = S::p0(1), P0 = S::p0(2);
@@ -188,34 +205,34 @@ __device__ __forceinline__ void slab_fwd(u64 (&r)[kElems], u64* sm, u32 tid, con
         sm_store<PP>(sm, tid, r);
         __syncthreads();
         sm_load<P0>(sm, tid, r);
-        fwd_round<S::top(2) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), q2, nq);
+        fwd_round<A, S::top(2) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
     }
 }
 
 // ---- inverse transform of a slab: the LOGS low stages, bottom bit first --------------------------
 // Entry layout: window at bit 0; exit layout: window at bit p0(0).
 // LAST: the slab is the whole polynomial (N == 2^LOGS), so the top stage folds N^-1.
-template <int LOGS, bool LAST>
-__device__ __forceinline__ void slab_inv(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 q2, u64 nq,
+template <class A, int LOGS, bool LAST>
+__device__ __forceinline__ void slab_inv(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 C, u64 nq,
                                          const LimbParams* __restrict__ Pg) {
     using S = Sched<LOGS>;
     if constexpr (S::NR > 2) {
         constexpr int P0 = S::p0(2), PN = S::p0(1);
-        inv_round<S::top(2) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), q2, nq, Pg);
+        inv_round<A, S::top(2) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
         __syncthreads();
         sm_load<PN>(sm, tid, r);
     }
     if constexpr (S::NR > 1) {
         constexpr int P0 = S::p0(1), PN = S::p0(0);
-        inv_round<S::top(1) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), q2, nq, Pg);
+        inv_round<A, S::top(1) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
         __syncthreads();
         sm_load<PN>(sm, tid, r);
     }
     {
         constexpr int P0 = S::p0(0);
-        inv_round<S::top(0) - 1 - P0, 0, LAST>(r, round_tw<P0>(T, off, tid), q2, nq, Pg);
+        inv_round<A, S::top(0) - 1 - P0, 0, LAST>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
     }
 }
 

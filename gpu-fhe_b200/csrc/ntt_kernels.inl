@@ -16,6 +16,8 @@
 // These kernels are what arithmetic.NTT / arithmetic.iNTT / polynomial.poly_mul dispatch to;
 // they replace the stubs at /root/reference/arithmetic.py:15-19 and the missing product in
 // /root/reference/" polynomial.py":3-5.
+// This file is a template body: ntt_harvey.cu and ntt_lazy.cu include it and instantiate Launcher<A>
+// for one arithmetic policy each (modarith.cuh), so the two sets of kernels compile in parallel.
 #include "ntt_core.cuh"
 #include "plan.h"
 
@@ -32,7 +34,7 @@ struct TileGeo {
 
 struct Tables {   // kernel argument: the plan's device tables
     const ulonglong2* tw;    // [L][N]
-    const ulonglong2* t0;    // [L][15][N/16]
+    const ulonglong2* t0;    // [L][N/512][15][32]
     const LimbParams* params;
 };
 
@@ -52,7 +54,22 @@ __device__ __forceinline__ TileId tile_id(u32 logN, u32 B, u32 limb0) {
 }
 __device__ __forceinline__ TwTab limb_tables(const Tables& T, u32 limb, u32 logN) {
     const size_t N = (size_t)1 << logN;
-    return TwTab{T.tw + limb * N, T.t0 + limb * (15 * (N >> 4)), (u32)N};
+    return TwTab{T.tw + limb * N, T.t0 + limb * t0_entries(N), (u32)N};
+}
+
+// Per-limb scalars every kernel needs: Cf/Ci = offset constants of the arithmetic policy.
+struct LimbK { u64 q, nq, Cf, Ci; };
+template <class A>
+__device__ __forceinline__ LimbK limb_consts(const LimbParams* __restrict__ Pg) {
+    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->q2));   // {2q, -q}
+    return LimbK{v.x >> 1, v.y, (u64)(A::kFwdC / 2) * v.x, (u64)(A::kInvC / 2) * v.x};
+}
+template <class A>
+__device__ __forceinline__ void fwd_final_all(u64 (&r)[kElems], const LimbK& K, const LimbParams* __restrict__ Pg) {
+    u32 ks = 0, km = 0;
+    if constexpr (A::kLazy) { ks = __ldg(&Pg->kshift); km = (u32)__ldg(&Pg->kmu); }
+#pragma unroll
+    for (int i = 0; i < kElems; ++i) r[i] = fwd_final<A>(r[i], K.q, K.nq, ks, km);
 }
 
 template <int LOGT>
@@ -78,22 +95,21 @@ __device__ __forceinline__ void copy_in_swizzled(u64* sm, const u64* in, u32 tid
 }
 
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
-template <int LOGS, int LOGT>
+template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     __shared__ __align__(16) u64 sm[1 << LOGT];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
-    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const LimbK K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
     u64 r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm, tid, T, s.off, q2, nq);
-#pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], q2), q2 >> 1);
+    slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
+    fwd_final_all<A>(r, K, Pg);
     if constexpr (LOGT > 4) {
         sm_store<0>(sm, tid, r);   // own 128-byte row: no hazard with the preceding sm_load<0>
         __syncthreads();
@@ -106,14 +122,14 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 
 // Inverse: the LOGS low stages (bottom first).  Always the first pass of an inverse NTT; when the
 // tile is the whole polynomial it also folds N^-1 and fully reduces.
-template <int LOGS, int LOGT, bool WHOLE>
+template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     __shared__ __align__(16) u64 sm[1 << LOGT];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
-    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const LimbK K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
     u64 r[kElems];
     if constexpr (LOGT > 4) {
@@ -124,7 +140,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + i];
     }
-    slab_inv<LOGS, WHOLE>(r, sm, tid, T, s.off, q2, nq, Pg);
+    slab_inv<A, LOGS, WHOLE>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) out[s.g0 + elem_index<P0>(tid, i)] = r[i];
@@ -132,7 +148,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 
 // Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
 // is the complete negacyclic product of one limb-polynomial in a single launch.
-template <int LOGS, int LOGT, bool WHOLE>
+template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
     extern __shared__ __align__(16) u64 smem[];
@@ -141,30 +157,30 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
-    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
+    const LimbK K = limb_consts<A>(Pg);
     const TwTab Tf = limb_tables(tf, s.limb, logN);
     const TwTab Ti = limb_tables(ti, s.limb, logN);
     constexpr int P0 = Sched<LOGS>::p0(0);
     u64 r[kElems];
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = a[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm0, tid, Tf, s.off, q2, nq);
-#pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = csub(csub(r[i], q2), q2 >> 1);
+    slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
+    fwd_final_all<A>(r, K, Pg);
     sm_store<0>(sm1, tid, r);   // private 128-byte row of sm1: written and read back by this thread only
     __syncthreads();            // every thread has finished reading a's last exchange out of sm0
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = b[s.g0 + elem_index<P0>(tid, i)];
-    slab_fwd<LOGS>(r, sm0, tid, Tf, s.off, q2, nq);
-    const u64 q = q2 >> 1, mu = __ldg(&Pg->bar_mu);
+    slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
+    fwd_final_all<A>(r, K, Pg);
+    const u64 mu = __ldg(&Pg->bar_mu);
     const u32 bs = __ldg(&Pg->bar_shift);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sm1 + swz((tid << 4) | (2 * j)));
-        r[2 * j] = barrett_mul(va.x, csub(csub(r[2 * j], q2), q), q, mu, bs);
-        r[2 * j + 1] = barrett_mul(va.y, csub(csub(r[2 * j + 1], q2), q), q, mu, bs);
+        r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
+        r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
     }
-    slab_inv<LOGS, WHOLE>(r, sm0, tid, Ti, s.off, q2, nq, Pg);
+    slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) c[s.g0 + elem_index<P0>(tid, i)] = r[i];
 }
@@ -173,82 +189,98 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
 // column kernels (N > 4096): tile = 2^T rows x C columns, T = 12 - LOGC, C = 2^LOGC, row stride 2^S;
 // tile index e = k*C + j  <->  coefficient k*2^S + tile*C + j.  Transform bits of e: [LOGC, 12).
 // Twiddles depend only on the row bits, so every tile of a limb reads the same 2^T - 1 entries.
+// S is a template parameter (8 or 12) so every register's global offset is an immediate.
 // ------------------------------------------------------------------------------------------------
-template <int LOGC>
+template <int LOGC, int S>
 struct ColGeo {
     static constexpr int LO8 = LOGC > 8 ? LOGC - 8 : 0;   // lowest local bit of the window at bit 8
     static constexpr int LO4 = LOGC > 4 ? LOGC - 4 : 0;   // lowest local bit of the window at bit 4
     static constexpr bool TWO = LOGC < 8;                  // needs the second window
-    __device__ static __forceinline__ u64 addr(u64 base, u32 e, u32 S) {
-        return base + (e & ((1u << LOGC) - 1u)) + ((u64)(e >> LOGC) << S);
-    }
+    static constexpr int LOGN = S + 12 - LOGC, LT = S - LOGC;   // 2^LT tiles per polynomial
+    // offset of tile element e from the tile base
+    __device__ static __forceinline__ u32 off(u32 e) { return (e & ((1u << LOGC) - 1u)) + ((e >> LOGC) << S); }
+    // off() moves bit fields, and the thread bits and register bits of elem_index<P0>(tid, i) are disjoint, so
+    // off(elem_index<P0>(tid, i)) = toff<P0>(tid) + roff<P0>(i) with roff a compile-time constant (an immediate).
+    __host__ __device__ static constexpr u32 off_c(u32 e) { return (e & ((1u << LOGC) - 1u)) + ((e >> LOGC) << S); }
+    template <int P0> __device__ static __forceinline__ u32 toff(u32 tid) { return off(elem_index<P0>(tid, 0)); }
+    template <int P0> __host__ __device__ static constexpr u32 roff(int i) { return off_c((u32)i << P0); }
 };
 struct ColId { u64 base; u32 limb; };
-template <int LOGC>
-__device__ __forceinline__ ColId col_id(u32 S, u32 B, u32 limb0) {
-    const u32 logN = S + 12 - LOGC, lt = S - LOGC;          // 2^lt tiles per polynomial
-    const u32 p = blockIdx.x >> lt, tile = blockIdx.x & ((1u << lt) - 1u);
-    return ColId{((u64)p << logN) + ((u64)tile << LOGC), limb0 + p / B};
+template <int LOGC, int S>
+__device__ __forceinline__ ColId col_id(u32 B, u32 limb0) {
+    using Geo = ColGeo<LOGC, S>;
+    const u32 p = blockIdx.x >> Geo::LT, tile = blockIdx.x & ((1u << Geo::LT) - 1u);
+    return ColId{((u64)p << Geo::LOGN) + ((u64)tile << LOGC), limb0 + p / B};
 }
 
-template <int LOGC>
+template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
-k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 S, u32 B, u32 limb0) {
-    using Geo = ColGeo<LOGC>;
+k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 B, u32 limb0) {
+    using Geo = ColGeo<LOGC, S>;
     __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
-    const u64* in = blockIdx.y ? in1 : in0;
-    u64* out = blockIdx.y ? out1 : out0;
     const u32 tid = threadIdx.x;
-    const ColId id = col_id<LOGC>(S, B, limb0);
+    const ColId id = col_id<LOGC, S>(B, limb0);
+    const u64* in = (blockIdx.y ? in1 : in0) + id.base;
+    u64* out = (blockIdx.y ? out1 : out0) + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
-    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
-    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << (S + 12 - LOGC));
+    const LimbK K = limb_consts<A>(Pg);
+    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << Geo::LOGN);
     u64 r[kElems];
+    {
+        const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<8>(tid, i), S)];
-    fwd_round<3, Geo::LO8>(r, TwStd{tw, 1u}, q2, nq);
+        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
+    }
+    fwd_round<A, 3, Geo::LO8>(r, TwStd{tw, 1u}, K.Cf, K.nq);
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
         __syncthreads();
         sm_load<4>(sm, tid, r);
-        fwd_round<3, Geo::LO4>(r, TwStd{tw, 16u + (tid >> 4)}, q2, nq);
+        fwd_round<A, 3, Geo::LO4>(r, TwStd{tw, 16u + (tid >> 4)}, K.Cf, K.nq);
+        u64* p = out + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<4>(tid, i), S)] = r[i];
+        for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = r[i];
     } else {
+        u64* p = out + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<8>(tid, i), S)] = r[i];
+        for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = r[i];
     }
 }
 
-template <int LOGC>
+template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
-k_col_inv(const u64* in, u64* out, const Tables tabs, u32 S, u32 B, u32 limb0) {
-    using Geo = ColGeo<LOGC>;
+k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
+    using Geo = ColGeo<LOGC, S>;
     __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
     const u32 tid = threadIdx.x;
-    const ColId id = col_id<LOGC>(S, B, limb0);
+    const ColId id = col_id<LOGC, S>(B, limb0);
+    const u64* in = in0 + id.base;
+    u64* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
-    const u64 q2 = __ldg(&Pg->q2), nq = __ldg(&Pg->nq);
-    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << (S + 12 - LOGC));
+    const LimbK K = limb_consts<A>(Pg);
+    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << Geo::LOGN);
     u64 r[kElems];
     if constexpr (Geo::TWO) {
+        const u64* p = in + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<4>(tid, i), S)];
-        inv_round<3, Geo::LO4, false>(r, TwStd{tw, 16u + (tid >> 4)}, q2, nq, Pg);
+        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<4>(i)];
+        inv_round<A, 3, Geo::LO4, false>(r, TwStd{tw, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
         sm_store<4>(sm, tid, r);
         __syncthreads();
         sm_load<8>(sm, tid, r);
     } else {
+        const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = in[Geo::addr(id.base, elem_index<8>(tid, i), S)];
+        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
     }
-    inv_round<3, Geo::LO8, true>(r, TwStd{tw, 1u}, q2, nq, Pg);
+    inv_round<A, 3, Geo::LO8, true>(r, TwStd{tw, 1u}, K.Ci, K.nq, Pg);
+    u64* p = out + Geo::template toff<8>(tid);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) out[Geo::addr(id.base, elem_index<8>(tid, i), S)] = r[i];
+    for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = r[i];
 }
 
 // ------------------------------------------------------------------------------------------------
-// host-side dispatch
+// host-side launchers, one set per arithmetic policy
 // ------------------------------------------------------------------------------------------------
 #define GFHE_ROW_CASES(X) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12)
 #define GFHE_COL_CASES(X) X(4) X(5) X(6) X(7)
@@ -264,112 +296,110 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
     return (unsigned)(((u64)nl * B) << (pl.logN - logT));
 }
 
-template <int LOGS>
-static void launch_row_fwd12(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
-    ProfScope ps(pl, K_ROW_FWD, st);
-    k_row_fwd<LOGS, 12><<<nt, 256, 0, st>>>(in, out, fwd_tables(pl), pl.logN, B, limb0);
-}
-template <int LOGS>
-static void launch_row_inv12(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
-    ProfScope ps(pl, K_ROW_INV, st);
-    k_row_inv<LOGS, 12, false><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0);
-}
-
-cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const unsigned nt = tiles_of(pl, nl, B);
-    if (pl.logN <= (u32)kMaxLogSlab) {
-        switch (pl.logN) {
-#define X(LS) case LS: { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<LS, LS><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, fwd_tables(pl), pl.logN, B, limb0); } break;
-            GFHE_ROW_CASES(X)
-#undef X
-            default: return cudaErrorInvalidValue;
-        }
-        return cudaGetLastError();
-    }
-    const u32 S = row_stages(pl.logN);
-    switch (12 - (int)(pl.logN - S)) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LC><<<dim3(nt, 1), 256, 0, st>>>(in, out, nullptr, nullptr, fwd_tables(pl), S, B, limb0); } break;
-        GFHE_COL_CASES(X)
-#undef X
-        default: return cudaErrorInvalidValue;
-    }
-    if (S == 8) launch_row_fwd12<8>(pl, limb0, out, out, B, nt, st);
-    else launch_row_fwd12<12>(pl, limb0, out, out, B, nt, st);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const unsigned nt = tiles_of(pl, nl, B);
-    if (pl.logN <= (u32)kMaxLogSlab) {
-        switch (pl.logN) {
-#define X(LS) case LS: { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<LS, LS, true><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0); } break;
-            GFHE_ROW_CASES(X)
-#undef X
-            default: return cudaErrorInvalidValue;
-        }
-        return cudaGetLastError();
-    }
-    const u32 S = row_stages(pl.logN);
-    if (S == 8) launch_row_inv12<8>(pl, limb0, in, out, B, nt, st);
-    else launch_row_inv12<12>(pl, limb0, in, out, B, nt, st);
-    switch (12 - (int)(pl.logN - S)) {
-#define X(LC) case LC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LC><<<nt, 256, 0, st>>>(out, out, inv_tables(pl), S, B, limb0); } break;
-        GFHE_COL_CASES(X)
-#undef X
-        default: return cudaErrorInvalidValue;
-    }
-    return cudaGetLastError();
-}
-
-template <int LOGS, int LOGT, bool WHOLE>
+template <class A, int LOGS, int LOGT, bool WHOLE>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
     const size_t smem = (size_t)2 * sizeof(u64) << LOGT;
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<LOGS, LOGT, WHOLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<A, LOGS, LOGT, WHOLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured[dev] = true;
     }
-    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<LOGS, LOGT, WHOLE><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
+    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<A, LOGS, LOGT, WHOLE><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
     return cudaGetLastError();
 }
 
-size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
-    if (pl.logN <= (u32)kMaxLogSlab) return 0;
-    return ((size_t)nl * B * sizeof(u64)) << pl.logN;   // one operand-sized scratch
+// column pass of a forward transform: in0 -> out0 and (if in1) in1 -> out1 in one launch
+template <class A>
+static cudaError_t launch_col_fwd(const Plan& pl, u32 limb0, const u64* in0, u64* out0, const u64* in1, u64* out1, u32 B,
+                                  unsigned nt, cudaStream_t st) {
+    const u32 S = row_stages(pl.logN);
+    const dim3 grid(nt, in1 ? 2 : 1);
+    ProfScope ps(pl, K_COL_FWD, st);
+    switch ((12 - (int)(pl.logN - S)) * 16 + (int)S) {
+#define X(LC) case LC * 16 + 8: k_col_fwd<A, LC, 8><<<grid, 256, 0, st>>>(in0, out0, in1, out1, fwd_tables(pl), B, limb0); break; \
+              case LC * 16 + 12: k_col_fwd<A, LC, 12><<<grid, 256, 0, st>>>(in0, out0, in1, out1, fwd_tables(pl), B, limb0); break;
+        GFHE_COL_CASES(X)
+#undef X
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaSuccess;
+}
+template <class A>
+static cudaError_t launch_col_inv(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
+    const u32 S = row_stages(pl.logN);
+    ProfScope ps(pl, K_COL_INV, st);
+    switch ((12 - (int)(pl.logN - S)) * 16 + (int)S) {
+#define X(LC) case LC * 16 + 8: k_col_inv<A, LC, 8><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), B, limb0); break; \
+              case LC * 16 + 12: k_col_inv<A, LC, 12><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), B, limb0); break;
+        GFHE_COL_CASES(X)
+#undef X
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaSuccess;
 }
 
-cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
+template <class A>
+cudaError_t Launcher<A>::ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
     const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
-#define X(LS) case LS: return launch_row_polymul<LS, LS, true>(pl, limb0, a, b, c, B, nt, st);
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_FWD, st); k_row_fwd<A, LS, LS><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, fwd_tables(pl), pl.logN, B, limb0); } break;
+            GFHE_ROW_CASES(X)
+#undef X
+            default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
+    if (cudaError_t e = launch_col_fwd<A>(pl, limb0, in, out, nullptr, nullptr, B, nt, st)) return e;
+    ProfScope ps(pl, K_ROW_FWD, st);
+    if (row_stages(pl.logN) == 8) k_row_fwd<A, 8, 12><<<nt, 256, 0, st>>>(out, out, fwd_tables(pl), pl.logN, B, limb0);
+    else k_row_fwd<A, 12, 12><<<nt, 256, 0, st>>>(out, out, fwd_tables(pl), pl.logN, B, limb0);
+    return cudaGetLastError();
+}
+
+template <class A>
+cudaError_t Launcher<A>::ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    const unsigned nt = tiles_of(pl, nl, B);
+    if (pl.logN <= (u32)kMaxLogSlab) {
+        switch (pl.logN) {
+#define X(LS) case LS: { ProfScope ps(pl, K_ROW_INV, st); k_row_inv<A, LS, LS, true><<<nt, TileGeo<LS>::NT, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0); } break;
+            GFHE_ROW_CASES(X)
+#undef X
+            default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
+    {
+        ProfScope ps(pl, K_ROW_INV, st);
+        if (row_stages(pl.logN) == 8) k_row_inv<A, 8, 12, false><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0);
+        else k_row_inv<A, 12, 12, false><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0);
+    }
+    if (cudaError_t e = launch_col_inv<A>(pl, limb0, out, out, B, nt, st)) return e;
+    return cudaGetLastError();
+}
+
+template <class A>
+cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
+                                  cudaStream_t st) {
+    const unsigned nt = tiles_of(pl, nl, B);
+    if (pl.logN <= (u32)kMaxLogSlab) {
+        switch (pl.logN) {
+#define X(LS) case LS: return launch_row_polymul<A, LS, LS, true>(pl, limb0, a, b, c, B, nt, st);
             GFHE_ROW_CASES(X)
 #undef X
             default: return cudaErrorInvalidValue;
         }
     }
     if (!ws) return cudaErrorInvalidValue;
-    const u32 S = row_stages(pl.logN);
-    const int LC = 12 - (int)(pl.logN - S);
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
-    switch (LC) {
-#define X(LCC) case LCC: { ProfScope ps(pl, K_COL_FWD, st); k_col_fwd<LCC><<<dim3(nt, 2), 256, 0, st>>>(a, c, b, ws, fwd_tables(pl), S, B, limb0); } break;
-        GFHE_COL_CASES(X)
-#undef X
-        default: return cudaErrorInvalidValue;
-    }
-    cudaError_t e = S == 8 ? launch_row_polymul<8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
-                           : launch_row_polymul<12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
+    if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, b, ws, B, nt, st)) return e;
+    cudaError_t e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
+                                             : launch_row_polymul<A, 12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
     if (e != cudaSuccess) return e;
-    switch (LC) {
-#define X(LCC) case LCC: { ProfScope ps(pl, K_COL_INV, st); k_col_inv<LCC><<<nt, 256, 0, st>>>(c, c, inv_tables(pl), S, B, limb0); } break;
-        GFHE_COL_CASES(X)
-#undef X
-        default: return cudaErrorInvalidValue;
-    }
+    if ((e = launch_col_inv<A>(pl, limb0, c, c, B, nt, st)) != cudaSuccess) return e;
     return cudaGetLastError();
 }
 

@@ -42,6 +42,10 @@ static void fill_limb_params(LimbParams& P, u64 q, u32 logN, u64 psi) {
     u128 mu = ((u128)1 << (k + 63)) / q;               // < 2^64 unless q is a power of two
     P.bar_mu = mu >> 64 ? ~0ull : (u64)mu;
     P.bar64 = (u64)((((u128)1) << 64) / q);
+    if (k >= 20) {
+        P.kshift = k - 17;
+        P.kmu = (u64)((((u128)1) << (32 + P.kshift)) / q);
+    }
     if (logN) {
         const u64 N = 1ull << logN;
         P.ninv = h_powmod(N % q, q - 2, q);
@@ -67,15 +71,15 @@ static void fill_tables(ulonglong2* fwd, ulonglong2* inv, u64 q, u32 logN, u64 p
     }
 }
 
-// t0[j][t] = std[(N >> (b+1)) + t * 2^(3-b) + hi],  j = (2^(3-b) - 1) + hi,  b = 0..3  (ntt_core.cuh, TwT0)
+// t0[t / 32][j][t % 32] = std[(N >> (b+1)) + t * 2^(3-b) + hi],  j = (2^(3-b) - 1) + hi,  b = 0..3  (ntt_core.cuh, TwT0)
 static void fill_t0(ulonglong2* t0, const ulonglong2* std_tab, u32 logN) {
     const u64 N = 1ull << logN, T = N >> 4;
     for (u32 b = 0; b < 4; ++b) {
         const u32 cnt = 1u << (3 - b);
         for (u32 hi = 0; hi < cnt; ++hi) {
-            ulonglong2* row = t0 + (size_t)((cnt - 1) + hi) * T;
+            const u32 j = (cnt - 1) + hi;
             const ulonglong2* src = std_tab + (N >> (b + 1)) + hi;
-            for (u64 t = 0; t < T; ++t) row[t] = src[t * cnt];
+            for (u64 t = 0; t < T; ++t) t0[(t >> 5) * kT0Block + j * 32 + (t & 31)] = src[t * cnt];
         }
     }
 }
@@ -97,6 +101,10 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     Plan* pl = new Plan();
     pl->device = device; pl->logN = logN; pl->L = L;
 
+    pl->lazy = true;
+    for (u32 l = 0; l < L; ++l) if (moduli[l] < (1ull << 19) || moduli[l] >= (1ull << 60)) pl->lazy = false;
+    if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->lazy = false;
+
     std::vector<LimbParams> hp(L);
     for (u32 l = 0; l < L; ++l) fill_limb_params(hp[l], moduli[l], logN, logN ? psi[l] : 0);
     if ((e = cudaMalloc(&pl->d_params, sizeof(LimbParams) * L)) != cudaSuccess) { plan_destroy(pl); return (int)e; }
@@ -104,10 +112,10 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
 
     if (logN) {
         const size_t N = (size_t)1 << logN, bytes = sizeof(ulonglong2) * N * L;
-        const size_t n0 = 15 * (N >> 4), bytes0 = sizeof(ulonglong2) * n0 * L;
+        const size_t n0 = t0_entries(N), bytes0 = sizeof(ulonglong2) * n0 * L;
         ulonglong2 *hf = nullptr, *hi = nullptr, *hf0 = nullptr, *hi0 = nullptr;
         hf = (ulonglong2*)std::malloc(bytes); hi = (ulonglong2*)std::malloc(bytes);
-        hf0 = (ulonglong2*)std::malloc(bytes0); hi0 = (ulonglong2*)std::malloc(bytes0);
+        hf0 = (ulonglong2*)std::calloc(bytes0, 1); hi0 = (ulonglong2*)std::calloc(bytes0, 1);
         if (!hf || !hi || !hf0 || !hi0) { std::free(hf); std::free(hi); std::free(hf0); std::free(hi0); plan_destroy(pl); return -6; }
         unsigned nthr = std::thread::hardware_concurrency();
         if (nthr == 0) nthr = 1;
@@ -136,6 +144,25 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     }
     *out = pl;
     return 0;
+}
+
+// ---- policy dispatch ---------------------------------------------------------------------------
+extern template struct Launcher<Harvey>;
+extern template struct Launcher<Lazy60>;
+
+cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    return pl.lazy ? Launcher<Lazy60>::ntt_fwd(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_fwd(pl, limb0, nl, in, out, B, st);
+}
+cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    return pl.lazy ? Launcher<Lazy60>::ntt_inv(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_inv(pl, limb0, nl, in, out, B, st);
+}
+cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
+    return pl.lazy ? Launcher<Lazy60>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st)
+                   : Launcher<Harvey>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
+}
+size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
+    if (pl.logN <= 12) return 0;
+    return ((size_t)nl * B * sizeof(u64)) << pl.logN;   // one operand-sized scratch
 }
 
 void host_pipe_destroy(Plan* p);   // capi.cu

@@ -25,11 +25,12 @@ struct Plan {
     int device = 0;
     u32 logN = 0;                      // 0: modulus set only (vec_* ops), no tables
     u32 L = 0;
+    bool lazy = false;                 // every modulus is in [2^19, 2^60): the Lazy60 kernels are used
     LimbParams* d_params = nullptr;    // [L]
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
-    ulonglong2* d_fwd_t0 = nullptr;    // [L][15][N/16] transposed copy of d_fwd for the window at bit 0
-    ulonglong2* d_inv_t0 = nullptr;    // [L][15][N/16] same for d_inv (ntt_core.cuh, TwT0)
+    ulonglong2* d_fwd_t0 = nullptr;    // [L][N/512][15][32] warp-tiled copy of d_fwd for the window at bit 0
+    ulonglong2* d_inv_t0 = nullptr;    // [L][N/512][15][32] same for d_inv (ntt_core.cuh, TwT0)
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
     Profiler* prof = nullptr;
 };
@@ -50,7 +51,16 @@ struct ProfScope {
 int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi);
 int plan_destroy(Plan* p);
 
-// ntt_kernels.cu -- all operate on limbs [limb0, limb0 + nl) of the plan; buffers are [nl, B, N]
+// ntt_kernels.inl, instantiated per arithmetic policy by ntt_harvey.cu / ntt_lazy.cu
+template <class A>
+struct Launcher {
+    static cudaError_t ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
+    static cudaError_t ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
+    static cudaError_t poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
+                                cudaStream_t st);
+};
+
+// plan.cu -- pick the policy of the plan; all operate on limbs [limb0, limb0 + nl), buffers are [nl, B, N]
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
 cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,

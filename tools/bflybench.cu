@@ -9,35 +9,6 @@ using namespace gfhe;
 
 constexpr int ITERS = 512, CH = 8;
 
-// approximate-high Shoup: h' in {h-2..h}, result in [0,4q) for any 64-bit x (5 WIDE + 4 IMAD)
-__device__ __forceinline__ u64 shoup_a(u64 x, u64 w, u64 ws, u64 nq) {
-    u64 r;
-    asm("{\n\t"
-        ".reg .u32 xl,xh,wl,wh,pl,ph,nl,nh,h0,h1,top,lo,d;\n\t"
-        ".reg .u64 t1,t2,h,acc;\n\t"
-        "mov.b64 {xl,xh}, %1;\n\t"
-        "mov.b64 {wl,wh}, %2;\n\t"
-        "mov.b64 {pl,ph}, %3;\n\t"
-        "mov.b64 {nl,nh}, %4;\n\t"
-        "mul.wide.u32 t1, xl, ph;\n\t"
-        "mov.b64 {d,h0}, t1;\n\t"
-        "cvt.u64.u32 t1, h0;\n\t"
-        "mad.wide.u32 t2, xh, pl, t1;\n\t"
-        "mov.b64 {d,h0}, t2;\n\t"
-        "cvt.u64.u32 t2, h0;\n\t"
-        "mad.wide.u32 h, xh, ph, t2;\n\t"
-        "mov.b64 {h0,h1}, h;\n\t"
-        "mul.wide.u32 acc, xl, wl;\n\t"
-        "mad.wide.u32 acc, h0, nl, acc;\n\t"
-        "mov.b64 {lo,top}, acc;\n\t"
-        "mad.lo.u32 top, xl, wh, top;\n\t"
-        "mad.lo.u32 top, xh, wl, top;\n\t"
-        "mad.lo.u32 top, h0, nh, top;\n\t"
-        "mad.lo.u32 top, h1, nl, top;\n\t"
-        "mov.b64 %0, {lo,top};\n\t"
-        "}\n" : "=l"(r) : "l"(x), "l"(w), "l"(ws), "l"(nq));
-    return r;
-}
 // high-word conditional subtraction: subtracts c when hi32(x) > hi32(c); result < max(c + 2^32, x - c)
 __device__ __forceinline__ u64 csub_hi(u64 x, u64 c) {
     u64 r;
@@ -61,6 +32,33 @@ __device__ __forceinline__ u64 dfmul(u64 x, u64 w0, u64 w1, double r0, double r1
     const u32 xl = (u32)x, xh = (u32)(x >> 32);
     const double ul = __hiloint2double(0x43300000, (int)xl) - 4503599627370496.0;
     const double uh = __hiloint2double(0x43300000, (int)xh) - 4503599627370496.0;
+    const double R = fma(ul, r0, fma(uh, r1, 4503599627370496.0));
+    const u32 hlo = (u32)__double2loint(R), hhi = (u32)__double2hiint(R);
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 al,ah,bl,bh,nl,nh,top,lo;\n\t"
+        ".reg .u64 acc;\n\t"
+        "mov.b64 {al,ah}, %3;\n\t"
+        "mov.b64 {bl,bh}, %4;\n\t"
+        "mov.b64 {nl,nh}, %5;\n\t"
+        "mul.wide.u32 acc, %1, al;\n\t"
+        "mad.wide.u32 acc, %2, bl, acc;\n\t"
+        "mad.wide.u32 acc, %6, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, %1, ah, top;\n\t"
+        "mad.lo.u32 top, %2, bh, top;\n\t"
+        "mad.lo.u32 top, %6, nh, top;\n\t"
+        "mad.lo.u32 top, %7, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n" : "=l"(r) : "r"(xl), "r"(xh), "l"(w0), "l"(w1), "l"(nq), "r"(hlo), "r"(hhi));
+    return r;
+}
+
+// same, but the two 32-bit halves are converted with I2F.F64.U32 (conversion pipe) instead of the
+// 2^52 bit trick (2 moves + 2 DADD)
+__device__ __forceinline__ u64 dfmul_cvt(u64 x, u64 w0, u64 w1, double r0, double r1, u64 nq) {
+    const u32 xl = (u32)x, xh = (u32)(x >> 32);
+    const double ul = __uint2double_rn(xl), uh = __uint2double_rn(xh);
     const double R = fma(ul, r0, fma(uh, r1, 4503599627370496.0));
     const u32 hlo = (u32)__double2loint(R), hhi = (u32)__double2hiint(R);
     u64 r;
@@ -133,6 +131,14 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
             } else if (MODE == 12) {  // approx shoup, csub on every second butterfly
                 const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i], t = shoup_a(Y[i], w, ws, nq);
                 X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 13) {  // FP64-assisted with I2F conversions, no csub
+                const u64 t = dfmul_cvt(Y[i], w, ws, r0, r1, nq);
+                const u64 x = X[i];
+                X[i] = x + t + q2; Y[i] = x - t + q4;
+            } else if (MODE == 14) {  // FP64-assisted with I2F conversions, csub every 2nd
+                const u64 t = dfmul_cvt(Y[i], w, ws, r0, r1, nq);
+                const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i];
+                X[i] = x + t + q2; Y[i] = x - t + q4;
             } else if (MODE == 7) {   // shoup_a alone
                 Y[i] = shoup_a(Y[i] + X[i], w, ws, nq);
             } else {                  // barrett product (pointwise)
@@ -192,6 +198,8 @@ int main() {
     run<10>("fwd  FP64-assisted, csub every 2nd", sms);
     run<11>("fwd  FP64-assisted, csub every bfly", sms);
     run<12>("fwd  approx shoup, csub every 2nd", sms);
+    run<13>("fwd  FP64-assisted (I2F), no csub", sms);
+    run<14>("fwd  FP64-assisted (I2F), csub every 2nd", sms);
     run<7>("shoup_a alone (+1 add)", sms);
     run<8>("barrett_mul (+2 csub)", sms);
     return 0;

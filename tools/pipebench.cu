@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(512, 2) k(u64* out, u32 seed) {
             if (OP == 13) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f[i]) : "f"(1.0000001f), "f"(0.5f));
             if (OP == 14) asm volatile("cvt.rn.f64.u64 %0, %1;" : "=d"(d[i]) : "l"(w[i] + (u64)d[i]));
             if (OP == 15) asm volatile("cvt.rzi.u64.f64 %0, %1;" : "=l"(w[i]) : "d"(d[i] + (double)w[i]));
+            if (OP == 20) asm volatile("cvt.rn.f64.u32 %0, %1;" : "=d"(d[i]) : "r"(a[i] + (u32)__double2loint(d[i])));
             if (OP == 16) asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(w[i]) : "l"(mn));
             if (OP == 17) asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(w[i]) : "l"(mn));
             if (OP == 18) asm volatile("add.f64 %0, %0, %1;" : "+d"(d[i]) : "d"(0.5));
@@ -88,6 +89,7 @@ int main(int argc, char** argv) {
     run<12>("IMAD.WIDE + DFMA interleaved", sms, 2);
     run<14>("I2F.F64.U64 (+add,+cvt back)", sms, 1);
     run<15>("F2I.U64.F64 (+add,+cvt back)", sms, 1);
+    run<20>("I2F.F64.U32 (+1 IADD)", sms, 1);
     run<16>("mul.lo.u64 (as compiled)", sms, 1);
     run<17>("mul.hi.u64 (as compiled)", sms, 1);
     return 0;

@@ -2,7 +2,7 @@
 //
 // A "slab" is 2^LOGS <= 4096 residues staged on one CTA: each thread owns 16 residues in
 // registers and runs up to four radix-2 stages ("a round") on them without touching memory;
-// between rounds the slab is re-distributed through XOR-swizzled shared memory.
+// between rounds the slab is re-distributed through row-padded shared memory.
 //
 //   forward : Cooley-Tukey, natural in -> bit-reversed out, lazy residues in [0, 4q) (Harvey) / [0,16q) (Lazy60)
 //   inverse : Gentleman-Sande, bit-reversed in -> natural out, lazy residues in [0, 2q) / [0, 8q),
@@ -22,9 +22,14 @@ namespace gfhe {
 constexpr int kElems = 16;       // residues per thread
 constexpr int kMaxLogSlab = 12;  // 4096 residues = 32 KiB per slab
 
-// 128-byte XOR swizzle at 16-byte-chunk granularity (same pattern as TMA SWIZZLE_128B):
-// chunk bits [1,4) of the residue index are XORed with row bits [4,7).
-__device__ __forceinline__ u32 swz(u32 e) { return e ^ (((e >> 4) & 7u) << 1); }
+// Shared-memory placement of slab residue e: every 16-residue row (128 bytes) is followed by 16 bytes of
+// padding, pad(e) = e + 2*(e/16) in 8-byte words.  A row-per-thread 16-byte access (window at bit 0) then
+// spreads its 32 lanes over all banks 4 lanes deep (the minimum for 512 bytes), the 8-byte accesses of the
+// other windows stay conflict-free -- and, unlike an XOR swizzle, pad() is ADDITIVE over disjoint bit fields:
+// pad(thread bits | register bits) = pad(thread bits) + pad(register bits), so every register's slot is one
+// per-thread base plus a compile-time immediate (no per-element address arithmetic, nothing to keep live).
+__host__ __device__ constexpr u32 pad(u32 e) { return e + ((e >> 4) << 1); }
+__host__ __device__ constexpr u32 padded_words(int logt) { return logt >= 4 ? pad(1u << logt) : (1u << logt); }
 
 // Residue index inside the slab of register i of thread tid when the thread's 4-bit window
 // sits at bit P0.
@@ -134,26 +139,27 @@ __device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 C, 
 // ---- shared-memory re-distribution ---------------------------------------------------------------
 template <int P0>
 __device__ __forceinline__ void sm_store(u64* sm, u32 tid, const u64 (&r)[kElems]) {
+    u64* p = sm + pad(elem_index<P0>(tid, 0));
     if constexpr (P0 == 0) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<ulonglong2*>(sm + swz((tid << 4) | (2 * j))) = make_ulonglong2(r[2 * j], r[2 * j + 1]);
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<ulonglong2*>(p + 2 * j) = make_ulonglong2(r[2 * j], r[2 * j + 1]);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) sm[swz(elem_index<P0>(tid, i))] = r[i];
+        for (int i = 0; i < kElems; ++i) p[pad((u32)i << P0)] = r[i];
     }
 }
 template <int P0>
 __device__ __forceinline__ void sm_load(const u64* sm, u32 tid, u64 (&r)[kElems]) {
+    const u64* p = sm + pad(elem_index<P0>(tid, 0));
     if constexpr (P0 == 0) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(sm + swz((tid << 4) | (2 * j)));
+            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + 2 * j);
             r[2 * j] = v.x; r[2 * j + 1] = v.y;
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = sm[swz(elem_index<P0>(tid, i))];
+        for (int i = 0; i < kElems; ++i) r[i] = p[pad((u32)i << P0)];
     }
 }
 

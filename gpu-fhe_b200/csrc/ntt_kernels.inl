@@ -2,7 +2,7 @@
 // RNS limbs, layout [L, B, N] (limb outermost, N contiguous), 8-byte residues.
 //
 // Work unit: a TILE of 4096 residues on one 256-thread CTA (16 residues per thread in registers,
-// four radix-2 stages per "round", rounds joined by an XOR-swizzled shared-memory exchange).
+// four radix-2 stages per "round", rounds joined by an row-padded shared-memory exchange).
 //
 // N <= 4096 : one kernel, one CTA per limb-polynomial (the tile is the polynomial).
 // N  > 4096 : two passes, N = 2^T x 2^S with S = 8 (N <= 2^16) or 12 (N <= 2^20), T = log2 N - S <= 8.
@@ -26,10 +26,13 @@ namespace gfhe {
 // ------------------------------------------------------------------------------------------------
 // row kernels: LOGS low stages on a contiguous tile of 2^LOGT residues (LOGS <= LOGT <= 12)
 // ------------------------------------------------------------------------------------------------
+#ifndef GFHE_MINB
+#define GFHE_MINB 2   // resident 256-thread CTAs per SM the 4096-residue kernels are compiled for (128 registers)
+#endif
 template <int LOGT>
 struct TileGeo {
     static constexpr int NT = LOGT > 4 ? (1 << (LOGT - 4)) : 1;
-    static constexpr int MINB = LOGT == 12 ? 2 : 1;   // 256-thread CTAs: cap at 128 registers
+    static constexpr int MINB = LOGT == 12 ? GFHE_MINB : 1;   // 256-thread CTAs: cap at 128 registers
 };
 
 struct Tables {   // kernel argument: the plan's device tables
@@ -73,16 +76,16 @@ __device__ __forceinline__ void fwd_final_all(u64 (&r)[kElems], const LimbK& K, 
 }
 
 template <int LOGT>
-__device__ __forceinline__ void copy_out_swizzled(const u64* sm, u64* out, u32 tid) {
+__device__ __forceinline__ void copy_out_padded(const u64* sm, u64* out, u32 tid) {
     constexpr int NT = TileGeo<LOGT>::NT;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
         const u32 e = 2u * (it * NT + tid);
-        *reinterpret_cast<ulonglong2*>(out + e) = *reinterpret_cast<const ulonglong2*>(sm + swz(e));
+        *reinterpret_cast<ulonglong2*>(out + e) = *reinterpret_cast<const ulonglong2*>(sm + pad(e));
     }
 }
 template <int LOGT>
-__device__ __forceinline__ void copy_in_swizzled(u64* sm, const u64* in, u32 tid) {
+__device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) {
     constexpr int NT = TileGeo<LOGT>::NT;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {   // two batches of four 16-byte loads in flight
@@ -90,7 +93,7 @@ __device__ __forceinline__ void copy_in_swizzled(u64* sm, const u64* in, u32 tid
 #pragma unroll
         for (int it = 0; it < 4; ++it) v[it] = *reinterpret_cast<const ulonglong2*>(in + 2u * ((4 * h + it) * NT + tid));
 #pragma unroll
-        for (int it = 0; it < 4; ++it) *reinterpret_cast<ulonglong2*>(sm + swz(2u * ((4 * h + it) * NT + tid))) = v[it];
+        for (int it = 0; it < 4; ++it) *reinterpret_cast<ulonglong2*>(sm + pad(2u * ((4 * h + it) * NT + tid))) = v[it];
     }
 }
 
@@ -98,7 +101,7 @@ __device__ __forceinline__ void copy_in_swizzled(u64* sm, const u64* in, u32 tid
 template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[1 << LOGT];
+    __shared__ __align__(16) u64 sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
@@ -107,13 +110,13 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     u64 r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + elem_index<P0>(tid, i)];
+    for (int i = 0; i < kElems; ++i) r[i] = (in + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     if constexpr (LOGT > 4) {
         sm_store<0>(sm, tid, r);   // own 128-byte row: no hazard with the preceding sm_load<0>
         __syncthreads();
-        copy_out_swizzled<LOGT>(sm, out + s.g0, tid);
+        copy_out_padded<LOGT>(sm, out + s.g0, tid);
     } else {
 #pragma unroll
         for (int i = 0; i < kElems; ++i) out[s.g0 + i] = r[i];
@@ -125,7 +128,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[1 << LOGT];
+    __shared__ __align__(16) u64 sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
@@ -133,7 +136,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     const TwTab T = limb_tables(tabs, s.limb, logN);
     u64 r[kElems];
     if constexpr (LOGT > 4) {
-        copy_in_swizzled<LOGT>(sm, in + s.g0, tid);
+        copy_in_padded<LOGT>(sm, in + s.g0, tid);
         __syncthreads();
         sm_load<0>(sm, tid, r);
     } else {
@@ -143,7 +146,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     slab_inv<A, LOGS, WHOLE>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) out[s.g0 + elem_index<P0>(tid, i)] = r[i];
+    for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = r[i];
 }
 
 // Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
@@ -153,7 +156,7 @@ __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
     extern __shared__ __align__(16) u64 smem[];
     u64* sm0 = smem;                 // exchange buffer
-    u64* sm1 = smem + (1 << LOGT);   // stash for NTT(a) while NTT(b) is computed
+    u64* sm1 = smem + padded_words(LOGT);   // stash for NTT(a) while NTT(b) is computed
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
@@ -163,26 +166,26 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     constexpr int P0 = Sched<LOGS>::p0(0);
     u64 r[kElems];
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = a[s.g0 + elem_index<P0>(tid, i)];
+    for (int i = 0; i < kElems; ++i) r[i] = (a + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     sm_store<0>(sm1, tid, r);   // private 128-byte row of sm1: written and read back by this thread only
     __syncthreads();            // every thread has finished reading a's last exchange out of sm0
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = b[s.g0 + elem_index<P0>(tid, i)];
+    for (int i = 0; i < kElems; ++i) r[i] = (b + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     const u64 mu = __ldg(&Pg->bar_mu);
     const u32 bs = __ldg(&Pg->bar_shift);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sm1 + swz((tid << 4) | (2 * j)));
+        const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sm1 + pad(tid << 4) + 2 * j);
         r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
         r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
     }
     slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) c[s.g0 + elem_index<P0>(tid, i)] = r[i];
+    for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = r[i];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -217,7 +220,7 @@ template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
 k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
-    __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
+    __shared__ __align__(16) u64 sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
     const u64* in = (blockIdx.y ? in1 : in0) + id.base;
@@ -251,7 +254,7 @@ template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
 k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
-    __shared__ __align__(16) u64 sm[Geo::TWO ? 4096 : 2];
+    __shared__ __align__(16) u64 sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
     const u64* in = in0 + id.base;
@@ -299,7 +302,7 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
 template <class A, int LOGS, int LOGT, bool WHOLE>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
-    const size_t smem = (size_t)2 * sizeof(u64) << LOGT;
+    const size_t smem = (size_t)2 * sizeof(u64) * padded_words(LOGT);
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {

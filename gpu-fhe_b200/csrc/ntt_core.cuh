@@ -61,6 +61,12 @@ struct TwStd {
     const ulonglong2* __restrict__ tw; u32 v;
     __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(tw + ((v << (3 - b)) + hi)); }
 };
+//  Sm   : the same indexing as Std, out of a copy of the table's first entries staged in shared memory (the
+//        column kernels: all tiles of a limb use entries [1, 2^T) only, 4 KB).
+struct TwSm {
+    const ulonglong2* s; u32 v;
+    __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return s[(v << (3 - b)) + hi]; }
+};
 struct TwT0 {
     const ulonglong2* __restrict__ p;                  // t0 + (t / 32) * kT0Block + t % 32
     __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(p + ((((1 << (3 - b)) - 1) + hi) << 5)); }

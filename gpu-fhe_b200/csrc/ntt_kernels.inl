@@ -227,19 +227,21 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
     u64* out = (blockIdx.y ? out1 : out0) + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK K = limb_consts<A>(Pg);
-    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << Geo::LOGN);
+    __shared__ ulonglong2 tws[256];
     u64 r[kElems];
     {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
     }
-    fwd_round<A, 3, Geo::LO8>(r, TwStd{tw, 1u}, K.Cf, K.nq);
+    tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
+    __syncthreads();
+    fwd_round<A, 3, Geo::LO8>(r, TwSm{tws, 1u}, K.Cf, K.nq);
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
         __syncthreads();
         sm_load<4>(sm, tid, r);
-        fwd_round<A, 3, Geo::LO4>(r, TwStd{tw, 16u + (tid >> 4)}, K.Cf, K.nq);
+        fwd_round<A, 3, Geo::LO4>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         u64* p = out + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = r[i];
@@ -261,22 +263,26 @@ k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     u64* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK K = limb_consts<A>(Pg);
-    const ulonglong2* tw = tabs.tw + ((size_t)id.limb << Geo::LOGN);
+    __shared__ ulonglong2 tws[256];
     u64 r[kElems];
     if constexpr (Geo::TWO) {
         const u64* p = in + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<4>(i)];
-        inv_round<A, 3, Geo::LO4, false>(r, TwStd{tw, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
-        sm_store<4>(sm, tid, r);
-        __syncthreads();
-        sm_load<8>(sm, tid, r);
     } else {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
     }
-    inv_round<A, 3, Geo::LO8, true>(r, TwStd{tw, 1u}, K.Ci, K.nq, Pg);
+    tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);
+    __syncthreads();
+    if constexpr (Geo::TWO) {
+        inv_round<A, 3, Geo::LO4, false>(r, TwSm{tws, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
+        sm_store<4>(sm, tid, r);
+        __syncthreads();
+        sm_load<8>(sm, tid, r);
+    }
+    inv_round<A, 3, Geo::LO8, true>(r, TwSm{tws, 1u}, K.Ci, K.nq, Pg);
     u64* p = out + Geo::template toff<8>(tid);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = r[i];

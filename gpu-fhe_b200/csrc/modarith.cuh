@@ -157,6 +157,26 @@ __device__ __forceinline__ u64 kred(u64 x, u32 kshift, u32 kmu, u64 nq) {
     return x + (u64)k * nq;
 }
 
+// Pointwise product for the Lazy60 pipeline: a, b < 2q  ->  a*b - Q'*q in [0, 6q) (measured < 3.5q), where the
+// quotient estimate Q' is the single-mulhi Barrett one taken with the approximate high product (deficit <= 2
+// more).  The 128-bit product shares its four partial products between the low and the high word, so the whole
+// thing is 8 IMAD.WIDE + 2 IMAD instead of two __umul64hi and two 64-bit multiplies; no final subtractions --
+// the inverse butterflies accept [0, 8q).
+__device__ __forceinline__ u64 mulhi_a(u64 x, u64 y) {
+    const u32 xl = (u32)x, xh = (u32)(x >> 32), yl = (u32)y, yh = (u32)(y >> 32);
+    return (u64)xh * yh + (((u64)xl * yh) >> 32) + (((u64)xh * yl) >> 32);
+}
+__device__ __forceinline__ u64 barrett_lazy(u64 a, u64 b, u64 nq, u64 mu, u32 s) {
+    const u32 al = (u32)a, ah = (u32)(a >> 32), bl = (u32)b, bh = (u32)(b >> 32);
+    const u64 p0 = (u64)al * bl, p3 = (u64)ah * bh;
+    const u64 m1 = (u64)al * bh + (p0 >> 32);          // < 2^64
+    const u64 m2 = (u64)ah * bl + (u32)m1;             // < 2^64
+    const u64 z0 = (m2 << 32) | (u32)p0;
+    const u64 z1 = p3 + (m1 >> 32) + (m2 >> 32);
+    const u64 x = (z0 >> s) | (z1 << (64 - s));        // floor(z / 2^(k-1)) < 2^(k+3)
+    return z0 + mulhi_a(x, mu) * nq;
+}
+
 // Arithmetic policies of the butterfly code (ntt_core.cuh).
 //   Harvey : exact Shoup, any q < 2^62.  forward residues in [0,4q), inverse in [0,2q).
 //   Lazy60 : approximate Shoup, 2^19 <= q < 2^60.  forward residues in [0,16q) with one conditional

@@ -99,6 +99,13 @@ __device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 C, 
     }
 }
 
+// Reduction of a forward residue that feeds the pointwise product: [0, 2q) is enough for Lazy60.
+template <class A>
+__device__ __forceinline__ u64 fwd_semi(u64 x, u64 q, u64 nq, u32 kshift, u32 kmu) {
+    if constexpr (A::kLazy) return kred(x, kshift, kmu, nq);
+    else return csub(csub(x, 2 * q), q);
+}
+
 // Full reduction of a forward residue to [0, q).
 template <class A>
 __device__ __forceinline__ u64 fwd_final(u64 x, u64 q, u64 nq, u32 kshift, u32 kmu) {

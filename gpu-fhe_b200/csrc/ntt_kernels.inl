@@ -75,6 +75,14 @@ __device__ __forceinline__ void fwd_final_all(u64 (&r)[kElems], const LimbK& K, 
     for (int i = 0; i < kElems; ++i) r[i] = fwd_final<A>(r[i], K.q, K.nq, ks, km);
 }
 
+template <class A>
+__device__ __forceinline__ void fwd_semi_all(u64 (&r)[kElems], const LimbK& K, const LimbParams* __restrict__ Pg) {
+    u32 ks = 0, km = 0;
+    if constexpr (A::kLazy) { ks = __ldg(&Pg->kshift); km = (u32)__ldg(&Pg->kmu); }
+#pragma unroll
+    for (int i = 0; i < kElems; ++i) r[i] = fwd_semi<A>(r[i], K.q, K.nq, ks, km);
+}
+
 template <int LOGT>
 __device__ __forceinline__ void copy_out_padded(const u64* sm, u64* out, u32 tid) {
     constexpr int NT = TileGeo<LOGT>::NT;
@@ -168,20 +176,28 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = (a + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
-    fwd_final_all<A>(r, K, Pg);
-    sm_store<0>(sm1, tid, r);   // private 128-byte row of sm1: written and read back by this thread only
+    fwd_semi_all<A>(r, K, Pg);
+    sm_store<0>(sm1, tid, r);   // private 144-byte row of sm1: written and read back by this thread only
     __syncthreads();            // every thread has finished reading a's last exchange out of sm0
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = (b + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
-    fwd_final_all<A>(r, K, Pg);
-    const u64 mu = __ldg(&Pg->bar_mu);
-    const u32 bs = __ldg(&Pg->bar_shift);
+    fwd_semi_all<A>(r, K, Pg);
+    {
+        const u64 mu = __ldg(&Pg->bar_mu);
+        const u32 bs = __ldg(&Pg->bar_shift);
+        const u64* pa = sm1 + pad(tid << 4);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(sm1 + pad(tid << 4) + 2 * j);
-        r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
-        r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
+        for (int j = 0; j < 8; ++j) {
+            const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(pa + 2 * j);
+            if constexpr (A::kLazy) {
+                r[2 * j] = barrett_lazy(va.x, r[2 * j], K.nq, mu, bs);
+                r[2 * j + 1] = barrett_lazy(va.y, r[2 * j + 1], K.nq, mu, bs);
+            } else {
+                r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
+                r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
+            }
+        }
     }
     slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
 #pragma unroll

@@ -157,6 +157,29 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = r[i];
 }
 
+// ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+// one thread: arm the barrier with the byte count and start the copy
+__device__ __forceinline__ void tma_tile_load(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
+    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+// every thread: wait for phase 0 of the barrier (the copy has landed and is visible)
+__device__ __forceinline__ void tma_tile_wait(u64* mbar) {
+    const u32 bar = smem_u32(mbar);
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "GFHE_TMA_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+        "@!p bra GFHE_TMA_WAIT;\n\t"
+        "}\n" ::"r"(bar) : "memory");
+}
+
 // Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
 // is the complete negacyclic product of one limb-polynomial in a single launch.
 template <class A, int LOGS, int LOGT, bool WHOLE>
@@ -165,8 +188,11 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     extern __shared__ __align__(16) u64 smem[];
     u64* sm0 = smem;                 // exchange buffer
     u64* sm1 = smem + padded_words(LOGT);   // stash for NTT(a) while NTT(b) is computed
+    u64* smb = sm1 + padded_words(LOGT);    // b's tile, fetched by one TMA bulk copy while a is transformed
+    u64* mbar = smb + (1 << LOGT);
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
+    if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(u64) << LOGT, mbar);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
     const LimbK K = limb_consts<A>(Pg);
     const TwTab Tf = limb_tables(tf, s.limb, logN);
@@ -178,9 +204,10 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
     sm_store<0>(sm1, tid, r);   // private 144-byte row of sm1: written and read back by this thread only
-    __syncthreads();            // every thread has finished reading a's last exchange out of sm0
+    __syncthreads();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
+    tma_tile_wait(mbar);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (b + s.g0 + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = (smb + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
     {
@@ -324,7 +351,7 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
 template <class A, int LOGS, int LOGT, bool WHOLE>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
-    const size_t smem = (size_t)2 * sizeof(u64) * padded_words(LOGT);
+    const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {

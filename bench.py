@@ -277,6 +277,35 @@ def run_b200(args, rank, world, local_rank):
     kernels = {names[i].decode(): {"ms_per_launch": tot[i] / cnt[i], "launches_per_step": cnt[i] / (K + 1)} for i in range(max(nk, 0))}
     # ---- forward NTT throughput (second half of the metric)
     ms_ntt = timed(step_ntt, K, W)
+    # ---- NTT-domain-resident kernels: pure HBM streaming, timed the same way
+    inner = nb * N
+    da4 = da.unsqueeze(0).expand(4, nl, nb, N).contiguous()
+    db4 = db.unsqueeze(0).expand(4, nl, nb, N).contiguous()
+
+    def step_mac(terms):
+        def f():
+            rc = lib.gfhe_ntt_mul_acc(plan.handle, 0, nl, inner, terms, da4.data_ptr(), db4.data_ptr(), nl * inner,
+                                      dc.data_ptr(), st)
+            if rc:
+                raise RuntimeError(_capi.error_string(rc))
+        return f
+
+    def step_auto():
+        rc = lib.gfhe_automorphism(plan.handle, 0, nl, nb, 5, 1, da.data_ptr(), dc.data_ptr(), st)
+        if rc:
+            raise RuntimeError(_capi.error_string(rc))
+
+    def step_vec_add():
+        rc = lib.gfhe_vec_add(plan.handle, 0, nl, inner, da.data_ptr(), db.data_ptr(), dc.data_ptr(), st)
+        if rc:
+            raise RuntimeError(_capi.error_string(rc))
+
+    Ks = max(5, min(K, 30))
+    ms_mac1 = timed(step_mac(1), Ks, W) / Ks
+    ms_mac4 = timed(step_mac(4), Ks, W) / Ks
+    ms_auto = timed(step_auto, Ks, W) / Ks
+    ms_vadd = timed(step_vec_add, Ks, W) / Ks
+    del da4, db4
     clocks.active = False
 
     # ---- e2e: host buffers through the C-ABI host entry point (pinned memory, copies inside)
@@ -347,6 +376,11 @@ def run_b200(args, rank, world, local_rank):
                      "share_of_step": dom_ms / step_kernel_ms if dom_ms and step_kernel_ms else None,
                      "whole_step": {"achieved": whole_gbs, "frac": whole_gbs / peak, "frac_of_8TBs_nominal": whole_gbs / 8000.0}},
         "kernels": kernels,
+        "ntt_domain": {
+            name: {"ms_per_launch": ms, "bytes_per_residue": bpr, "achieved_GBs": bpr * UNITS_PER_GPU * N / (ms * 1e-3) / 1e9,
+                   "frac": bpr * UNITS_PER_GPU * N / (ms * 1e-3) / 1e9 / peak}
+            for name, ms, bpr in (("mul_acc_terms1", ms_mac1, 24), ("mul_acc_terms4", ms_mac4, 72),
+                                  ("automorphism_ntt", ms_auto, 16), ("vec_add", ms_vadd, 24))},
         "ntt": {"metric": "limb_ntt_per_s", "value": ntt_value, "unit": "limb-NTT/s", "ms_per_step": ms_ntt / K,
                 "achieved_GBs": ntt_gbs, "frac": ntt_gbs / peak, "frac_of_8TBs_nominal": ntt_gbs / 8000.0},
         "e2e": {"value": units * e2e_steps / e2e_s, "unit": "limb-poly-mul/s", "steps": e2e_steps,

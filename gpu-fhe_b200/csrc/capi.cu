@@ -41,6 +41,8 @@ const char* gfhe_error_string(int code) {
         case GFHE_ERANGE: return "limb range outside the plan";
         case GFHE_EWORKSPACE: return "workspace missing or too small";
         case GFHE_ENOTABLES: return "plan has no NTT tables (created with log2_n = 0)";
+        case GFHE_ETERMS: return "too many terms: terms * q^2 must fit 128 bits";
+        case GFHE_EGALOIS: return "Galois element must be odd";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown gpufhe_b200 error";
     }
 }
@@ -72,7 +74,7 @@ int gfhe_profile_enable(gfhe_plan_t plan, int on) {
     return 0;
 }
 
-static const char* const kKernelNames[K_COUNT] = {"k_col_fwd", "k_row_fwd", "k_row_inv", "k_col_inv", "k_row_polymul", "k_vec"};
+static const char* const kKernelNames[K_COUNT] = {"k_col_fwd", "k_row_fwd", "k_row_inv", "k_col_inv", "k_row_polymul", "k_vec", "k_mul_acc", "k_automorphism"};
 
 int gfhe_profile_read(gfhe_plan_t plan, uint32_t max_kernels, const char** names, double* total_ms, uint64_t* launches) {
     if (!plan) return GFHE_EARG;
@@ -136,6 +138,30 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
     DeviceGuard g(P(plan)->device);
     return (int)launch_poly_mul(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b, (u64*)d_c, (u64*)d_ws, batch,
                                 S(stream));
+}
+
+int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner, uint32_t terms,
+                     const uint64_t* d_a, const uint64_t* d_b, uint64_t term_stride, uint64_t* d_out, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (inner == 0) return 0;
+    if (!d_a || !d_b || !d_out || terms == 0) return GFHE_EARG;
+    if (terms > 1 && (d_out == d_a || d_out == d_b)) return GFHE_EARG;
+    const uint32_t spare = 128u - 2u * P(plan)->max_bits;   // q < 2^62, so spare >= 4
+    const uint32_t max_terms = spare >= 16 ? 65536u : (1u << spare);
+    if (terms > max_terms) return GFHE_ETERMS;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_mul_acc(*P(plan), limb0, nl, inner, terms, (const u64*)d_a, (const u64*)d_b, term_stride, (u64*)d_out,
+                               S(stream));
+}
+
+int gfhe_automorphism(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch, uint32_t k, int ntt_domain,
+                      const uint64_t* d_in, uint64_t* d_out, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (!d_in || !d_out || batch == 0 || d_in == d_out) return GFHE_EARG;
+    if (P(plan)->logN == 0) return GFHE_ENOTABLES;
+    if ((k & 1u) == 0) return GFHE_EGALOIS;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_automorphism(*P(plan), limb0, nl, batch, k, ntt_domain != 0, (const u64*)d_in, (u64*)d_out, S(stream));
 }
 
 static int vec_op(int op, gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner,

@@ -28,7 +28,7 @@ struct __align__(16) LimbParams {
     u32 bar_shift;  // k - 1
     u32 kshift;     // k - 17 (kred: y = x >> kshift fits 32 bits for x < 16q); valid when k >= 20
     u64 kmu;        // floor(2^(32 + kshift) / q) <= 2^16
-    u64 pad;
+    u64 r64;        // 2^64 mod q (folds the high word of a 128-bit accumulator, ring_kernels.cu)
 };
 static_assert(sizeof(LimbParams) == 96, "LimbParams layout");
 

@@ -42,6 +42,7 @@ static void fill_limb_params(LimbParams& P, u64 q, u32 logN, u64 psi) {
     u128 mu = ((u128)1 << (k + 63)) / q;               // < 2^64 unless q is a power of two
     P.bar_mu = mu >> 64 ? ~0ull : (u64)mu;
     P.bar64 = (u64)((((u128)1) << 64) / q);
+    P.r64 = (u64)((((u128)1) << 64) % q);
     if (k >= 20) {
         P.kshift = k - 17;
         P.kmu = (u64)((((u128)1) << (32 + P.kshift)) / q);
@@ -102,6 +103,7 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     pl->device = device; pl->logN = logN; pl->L = L;
 
     pl->lazy = true;
+    for (u32 l = 0; l < L; ++l) { const u32 k = 64 - (u32)__builtin_clzll(moduli[l]); if (k > pl->max_bits) pl->max_bits = k; }
     for (u32 l = 0; l < L; ++l) if (moduli[l] < (1ull << 19) || moduli[l] >= (1ull << 60)) pl->lazy = false;
     if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->lazy = false;
 

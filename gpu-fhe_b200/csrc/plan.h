@@ -9,7 +9,7 @@ namespace gfhe {
 
 // Optional per-kernel timing (gfhe_profile_enable): every launch is bracketed by cudaEvents on
 // its own stream, so bench.py can report each kernel's live duration and share of the step.
-enum KernelId { K_COL_FWD = 0, K_ROW_FWD, K_ROW_INV, K_COL_INV, K_ROW_POLYMUL, K_VEC, K_COUNT };
+enum KernelId { K_COL_FWD = 0, K_ROW_FWD, K_ROW_INV, K_COL_INV, K_ROW_POLYMUL, K_VEC, K_MAC, K_AUTO, K_COUNT };
 struct Profiler {
     bool on = false;
     struct Rec { int kid; cudaEvent_t a, b; };
@@ -25,6 +25,7 @@ struct Plan {
     int device = 0;
     u32 logN = 0;                      // 0: modulus set only (vec_* ops), no tables
     u32 L = 0;
+    u32 max_bits = 0;                  // bit length of the largest modulus
     bool lazy = false;                 // every modulus is in [2^19, 2^60): the Lazy60 kernels are used
     LimbParams* d_params = nullptr;    // [L]
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
@@ -70,5 +71,11 @@ size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B);
 // vec_kernels.cu
 cudaError_t launch_vec_op(int op, const Plan& pl, u32 limb0, u32 nl, const long long* a, const long long* b,
                           long long* out, u64 inner, cudaStream_t st);
+
+// ring_kernels.cu -- NTT-domain multiply-accumulate and the Galois automorphism X -> X^k
+cudaError_t launch_mul_acc(const Plan& pl, u32 limb0, u32 nl, u64 inner, u32 terms, const u64* a, const u64* b,
+                           u64 term_stride, u64* out, cudaStream_t st);
+cudaError_t launch_automorphism(const Plan& pl, u32 limb0, u32 nl, u32 B, u32 k, bool ntt_domain, const u64* in, u64* out,
+                                cudaStream_t st);
 
 }  // namespace gfhe

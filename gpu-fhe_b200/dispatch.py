@@ -171,6 +171,58 @@ def poly_mul(a, b, MOD):
     return A.wrap(out)
 
 
+# ---- NTT-domain-resident ops ------------------------------------
+
+def mul_acc(a, b, MOD, stacked: bool):
+    """sum_t a[t] * b[t] mod q per limb.  a, b: [K, L, B, N] stacks (or sequences of K [L, B, N] operands) of canonical
+    NTT-domain residues; returns [L, B, N].  A [L, B, N] pair (no leading K) is the plain pointwise product."""
+    moduli = ring.resolve_moduli(MOD)
+    if isinstance(a, (list, tuple)):
+        a = torch.stack([_Arg(x).t for x in a]) if not isinstance(a[0], np.ndarray) else np.stack(a)
+    if isinstance(b, (list, tuple)):
+        b = torch.stack([_Arg(x).t for x in b]) if not isinstance(b[0], np.ndarray) else np.stack(b)
+    A = _Arg(a)
+    Bv = _Arg(b, A.t.device)
+    if A.shape != Bv.shape:
+        raise AssertionError("operands must have equal shapes")
+    L = len(moduli)
+    shape = A.shape
+    if stacked:
+        if len(shape) < 2 or shape[0] == 0:
+            raise ValueError("expected a non-empty leading term axis ([K, L, B, N]); got shape %s" % (shape,))
+        K, item = int(shape[0]), shape[1:]
+    else:
+        K, item = 1, shape
+    Lq, Bq, N = _lbn(item, L)
+    inner = Bq * N
+    dev = A.t.device
+    plan = ring.get_plan(dev.index, 0, moduli)
+    out = torch.empty(item, dtype=A.t.dtype, device=dev)
+    if inner == 0:
+        return A.wrap(out)
+    _capi.check(_capi.lib.gfhe_ntt_mul_acc(plan.handle, 0, Lq, inner, K, _ptr(A.t), _ptr(Bv.t), Lq * inner, _ptr(out),
+                                           _stream(dev)), "gfhe_ntt_mul_acc")
+    return A.wrap(out)
+
+
+def automorphism(x, k: int, MOD, ntt_domain: bool):
+    """a(X) -> a(X^k), k odd, on every limb-polynomial of x ([L, B, N]); out of place."""
+    moduli = ring.resolve_moduli(MOD)
+    X = _Arg(x)
+    L, B, N = _lbn(X.shape, len(moduli))
+    k = int(k) % (2 * N)
+    if k % 2 == 0:
+        raise ValueError("Galois element k must be odd, got %d" % k)
+    dev = X.t.device
+    plan = ring.get_plan(dev.index, N, moduli)
+    out = torch.empty_like(X.t)
+    if B == 0:
+        return X.wrap(out)
+    _capi.check(_capi.lib.gfhe_automorphism(plan.handle, 0, L, B, k, int(bool(ntt_domain)), _ptr(X.t), _ptr(out),
+                                            _stream(dev)), "gfhe_automorphism")
+    return X.wrap(out)
+
+
 # ---- host-buffer entry points (what bench.py's e2e leg times) ---------------------------------------
 
 def _host_u64(a: np.ndarray) -> np.ndarray:

@@ -11,6 +11,9 @@
  *   gfhe_ntt_inverse             <- /root/reference/arithmetic.py:18-19  (iNTT, an identity stub there)
  *   gfhe_plan_create             <- /root/reference/primitive.py:3-4     (placeholder for the roots of unity)
  *   gfhe_poly_mul                <- /root/reference/" polynomial.py":3-5 (module that would hold poly_mul)
+ *   gfhe_ntt_mul_acc             <- /root/reference/arithmetic.py:11-13 applied in the NTT domain (sum of pointwise
+ *                                   products; the reference has no NTT-domain API -- SURVEY.md section 8f row 2)
+ *   gfhe_automorphism            <- absent from the reference: a(X) -> a(X^k)
  *   gfhe_*_host                  <- the same calls made with host (numpy) arrays, as the reference's
  *                                   callers would make them; copies are pipelined inside the call
  *
@@ -34,7 +37,7 @@
 extern "C" {
 #endif
 
-#define GFHE_ABI_VERSION 1
+#define GFHE_ABI_VERSION 2
 
 #define GFHE_EARG      (-1)   /* null pointer / zero size */
 #define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
@@ -45,6 +48,8 @@ extern "C" {
 #define GFHE_ERANGE    (-7)   /* limb range outside the plan */
 #define GFHE_EWORKSPACE (-8)  /* workspace missing or too small */
 #define GFHE_ENOTABLES (-9)   /* plan was created without NTT tables (log2_n == 0) */
+#define GFHE_ETERMS    (-10)  /* too many terms: terms * q^2 must fit 128 bits */
+#define GFHE_EGALOIS   (-11)  /* Galois element must be odd */
 
 typedef struct gfhe_plan* gfhe_plan_t;   /* opaque; one per (device, N, modulus chain) */
 
@@ -82,6 +87,20 @@ int gfhe_vec_sub(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t 
                  const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
 int gfhe_vec_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
                  const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
+
+/* NTT-domain multiply-accumulate: out[l, i] = sum_{t < terms} a[t*term_stride + l*inner + i] * b[same] mod q_l.
+ * a, b hold `terms` arrays of layout [num_limbs, inner] (inner = batch * N) spaced term_stride words apart; inputs
+ * must be canonical residues in [0, q) (what gfhe_ntt_forward writes).  terms == 1 is the pointwise product.
+ * Products are accumulated in 128 bits and reduced once: terms * q^2 must be < 2^128 (GFHE_ETERMS otherwise;
+ * 256 terms for 60-bit moduli).  out may alias a or b only when terms == 1. */
+int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner, uint32_t terms,
+                     const uint64_t* d_a, const uint64_t* d_b, uint64_t term_stride, uint64_t* d_out, void* stream);
+
+/* Galois automorphism a(X) -> a(X^k) of every limb-polynomial, k odd (taken mod 2N).  ntt_domain == 0: coefficient
+ * domain in and out (signed index permutation); ntt_domain != 0: both in the bit-reversed evaluation order of
+ * gfhe_ntt_forward (pure permutation), so that automorphism(NTT(a)) == NTT(automorphism(a)).  Out of place. */
+int gfhe_automorphism(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch, uint32_t k, int ntt_domain,
+                      const uint64_t* d_in, uint64_t* d_out, void* stream);
 
 /* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan
  * (pinned memory gives full PCIe rate; pageable works).  Limb groups are streamed

@@ -276,3 +276,37 @@ def ntt_point(x, q: int, psi: int, k: int) -> int:
 
 def random_poly(rng: random.Random, N: int, q: int) -> List[int]:
     return [rng.randrange(q) for _ in range(N)]
+
+
+# ---- NTT-domain inner product and Galois automorphism -------------------
+# The reference has neither; these restate the definitions in Python ints.
+
+def mul_acc(a_terms: Sequence[Sequence[int]], b_terms: Sequence[Sequence[int]], q: int) -> List[int]:
+    """out[i] = sum_t a_terms[t][i] * b_terms[t][i] mod q."""
+    n = len(a_terms[0])
+    return [sum(int(a[i]) * int(b[i]) for a, b in zip(a_terms, b_terms)) % q for i in range(n)]
+
+
+def automorphism_coeff(a: Sequence[int], k: int, q: int) -> List[int]:
+    """Coefficients of a(X^k) mod (X^N + 1, q), k odd: a_i X^(ik), with X^N = -1."""
+    N = len(a)
+    out = [0] * N
+    for i, v in enumerate(a):
+        e = (i * k) % (2 * N)
+        if e < N:
+            out[e] = int(v) % q
+        else:
+            out[e - N] = (-int(v)) % q
+    return out
+
+
+def automorphism_ntt(X: Sequence[int], k: int) -> List[int]:
+    """The same map on NTT(a) in bit-reversed evaluation order: position j holds a(psi^(2 brv(j) + 1)), and
+    (sigma_k a)(psi^e) = a(psi^(k e))."""
+    N = len(X)
+    bits = N.bit_length() - 1
+    out = [0] * N
+    for j in range(N):
+        e = (k * (2 * brv(j, bits) + 1)) % (2 * N)
+        out[j] = X[brv((e - 1) // 2, bits)]
+    return out

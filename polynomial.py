@@ -7,13 +7,16 @@ cannot be imported by name; this one can).
     poly_sub(a, b, MOD)   same shape of call, difference
     poly_mul(a, b, MOD)   new: negacyclic product in Z_q[X]/(X^N+1) per RNS limb,
                           iNTT(NTT(a) * NTT(b)) as one fused GPU pipeline
+    poly_mul_ntt(A, B)    NTT-domain pointwise product of operands that are already transformed
+    poly_mac_ntt(As, Bs)  NTT-domain inner product sum_t As[t] * Bs[t] (key-switching style), one reduction per residue
+    automorphism(x, k)    Galois map a(X) -> a(X^k), coefficient domain or (ntt=True) NTT domain
 """
 from primitive import *  # noqa: F401,F403
 from arithmetic import _d
 
 __all__ = ["np", "vec_add", "vec_sub", "vec_mul", "NTT", "iNTT", "XXX",
            "find_psi", "ntt_primes", "is_probable_prime", "set_ring", "get_ring", "ring", "make_plan", "clear_plans",
-           "poly_add", "poly_sub", "poly_mul"]
+           "poly_add", "poly_sub", "poly_mul", "poly_mul_ntt", "poly_mac_ntt", "automorphism"]
 
 
 def poly_add(a, b, MOD):
@@ -29,3 +32,20 @@ def poly_mul(a, b, MOD=None):
     [L,1,1] array, or None to use the installed ring."""
     assert a.shape == b.shape
     return _d.poly_mul(a, b, MOD)
+
+
+def poly_mul_ntt(a, b, MOD=None):
+    """NTT(a*b) from NTT(a), NTT(b): [L, B, N] canonical residues in, same out."""
+    assert a.shape == b.shape
+    return _d.mul_acc(a, b, MOD, False)
+
+
+def poly_mac_ntt(a, b, MOD=None):
+    """sum_t a[t] * b[t] in the NTT domain.  a, b: [K, L, B, N] stacks or length-K sequences of [L, B, N]."""
+    return _d.mul_acc(a, b, MOD, True)
+
+
+def automorphism(x, k, *, ntt=False, MOD=None):
+    """a(X) -> a(X^k) for odd k; with ntt=True x and the result are in NTT(x)'s evaluation order, and
+    automorphism(NTT(a), k, ntt=True) == NTT(automorphism(a, k))."""
+    return _d.automorphism(x, k, MOD, ntt)

@@ -360,3 +360,82 @@ def test_sharded_equals_unsharded(cuda_device):
             part = P.poly_mul(shard.take(ta, sh), shard.take(tb, sh), list(moduli[sh.limbs[0]:sh.limbs[1]]))
             out[sh.limbs[0]:sh.limbs[1], sh.batch[0]:sh.batch[1]] = part
         assert torch.equal(out, full), world
+
+
+# ---------------------------------------------------------------------------------------------------
+# NTT-domain-resident ops: inner product and Galois automorphism
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("bits,K", [(30, 1), (50, 3), (60, 7), (60, 256), (61, 16)])
+def test_ntt_mul_acc_matches_python_ints(cuda_device, bits, K):
+    import polynomial as P
+    L, B, N = 3, 2, 64
+    moduli = O.ntt_primes(bits, L)
+    rng = np.random.default_rng(bits * 1000 + K)
+    a = np.stack([np.stack([rng.integers(0, q, (B, N), dtype=np.uint64) for q in moduli]) for _ in range(K)])
+    b = np.stack([np.stack([rng.integers(0, q, (B, N), dtype=np.uint64) for q in moduli]) for _ in range(K)])
+    a[0, :, 0, :4] = np.array([[q - 1] * 4 for q in moduli], dtype=np.uint64)   # extremes: (q-1)^2 in every term slot 0
+    b[0, :, 0, :4] = np.array([[q - 1] * 4 for q in moduli], dtype=np.uint64)
+    got = host_u64(P.poly_mac_ntt(dev_i64(a, cuda_device), dev_i64(b, cuda_device), MOD=moduli))
+    assert got.shape == (L, B, N)
+    for l, q in enumerate(moduli):
+        want = O.mul_acc([a[t, l].ravel().tolist() for t in range(K)], [b[t, l].ravel().tolist() for t in range(K)], q)
+        assert got[l].ravel().tolist() == want, (bits, K, l)
+    if K == 1:   # un-stacked form == vec_mul on canonical residues
+        import arithmetic as A
+        g1 = P.poly_mul_ntt(dev_i64(a[0], cuda_device), dev_i64(b[0], cuda_device), MOD=moduli)
+        g2 = A.vec_mul(dev_i64(a[0], cuda_device), dev_i64(b[0], cuda_device), col(moduli))
+        assert torch.equal(g1, g2) and np.array_equal(host_u64(g1), got)
+
+
+def test_ntt_mul_acc_too_many_terms_is_an_error(cuda_device):
+    import polynomial as P
+    from gpu_fhe_b200 import _capi
+    q = O.ntt_primes(61, 1)[0]   # 61-bit modulus: 2^(128-122) = 64 terms at most
+    x = torch.zeros((65, 1, 1, 16), dtype=torch.int64, device=cuda_device)
+    with pytest.raises(_capi.GpuFheError) as ei:
+        P.poly_mac_ntt(x, x, MOD=[q])
+    assert ei.value.code == -10
+
+
+def test_poly_mul_equals_intt_of_ntt_domain_product(cuda_device):
+    import polynomial as P
+    N, L, B = 8192, 2, 3
+    moduli = O.ntt_primes(60, L)
+    a, b = rand_lbn(11, moduli, B, N), rand_lbn(12, moduli, B, N)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    with P.ring(moduli):
+        c = P.poly_mul(ta, tb)
+        c2 = P.iNTT(P.poly_mul_ntt(P.NTT(ta), P.NTT(tb)))
+        # inner product of two terms == sum of the two products
+        s = P.iNTT(P.poly_mac_ntt([P.NTT(ta), P.NTT(tb)], [P.NTT(tb), P.NTT(tb)]))
+        want = P.vec_add(P.poly_mul(ta, tb), P.poly_mul(tb, tb), col(moduli))
+    assert torch.equal(c, c2)
+    assert torch.equal(s, want)
+
+
+@pytest.mark.parametrize("logn", [4, 8, 12, 16])
+def test_automorphism_both_domains(cuda_device, logn):
+    import polynomial as P
+    N, L, B = 1 << logn, 2, 2
+    moduli = O.ntt_primes(60, L)
+    a = rand_lbn(logn, moduli, B, N)
+    a[:, :, 1] = 0   # zero coefficients must stay zero under negation (not become q)
+    ta = dev_i64(a, cuda_device)
+    for k in (3, 5, 2 * N - 1, N + 1, 1, 2 * N + 3):
+        with P.ring(moduli):
+            c = P.automorphism(ta, k)
+            cn = P.automorphism(P.NTT(ta), k, ntt=True)
+            assert torch.equal(P.NTT(c), cn), (logn, k)          # commutes with the transform
+        h = host_u64(c)
+        for l, q in enumerate(moduli):
+            want = O.automorphism_coeff(a[l, 0].tolist(), k % (2 * N), q)
+            assert h[l, 0].tolist() == want, (logn, k, l)
+    if logn <= 8:   # NTT-domain permutation against the definition-level oracle
+        q = moduli[0]
+        psi = O.find_psi(q, N)
+        X = O.ntt_definition(a[0, 0].tolist(), q, psi)
+        with P.ring(moduli):
+            got = host_u64(P.automorphism(P.NTT(ta), 5, ntt=True))[0, 0].tolist()
+        assert got == O.automorphism_ntt(X, 5)
+    with pytest.raises(ValueError):
+        P.automorphism(ta, 4, MOD=moduli)

@@ -120,3 +120,35 @@ def test_c_oracle_properties(logn, bits):
     if N <= 128:
         for l, q in enumerate(qs):
             assert c[l, 0].tolist() == O.schoolbook_negacyclic(a[l, 0].tolist(), b[l, 0].tolist(), q)
+
+
+# ---- NTT-domain inner product and automorphism oracles ------------------
+@pytest.mark.parametrize("N,bits", [(16, 30), (64, 50), (256, 60)])
+def test_automorphism_oracles_agree_with_definition(N, bits):
+    q = O.ntt_primes(bits, 1)[0]
+    psi = O.find_psi(q, N)
+    rng = random.Random(N)
+    a = O.random_poly(rng, N, q)
+    for k in (3, 5, 2 * N - 1, N + 1, 1):
+        c = O.automorphism_coeff(a, k, q)
+        # definition: (sigma_k a)(x) = a(x^k) at every root of X^N + 1
+        for j in (0, 1, N // 2, N - 1):
+            pt = pow(psi, 2 * j + 1, q)
+            assert O._horner(c, pt, q) == O._horner(a, pow(pt, k, q), q)
+        # the NTT-domain permutation commutes with the transform
+        assert O.automorphism_ntt(O.ntt_definition(a, q, psi), k) == O.ntt_definition(c, q, psi)
+    # sigma_k is a ring homomorphism: sigma(a*b) = sigma(a)*sigma(b)
+    b = O.random_poly(rng, N, q)
+    assert O.automorphism_coeff(O.schoolbook_negacyclic(a, b, q), 5, q) == \
+        O.schoolbook_negacyclic(O.automorphism_coeff(a, 5, q), O.automorphism_coeff(b, 5, q), q)
+
+
+def test_mul_acc_oracle_is_the_sum_of_reference_style_products():
+    q = O.ntt_primes(60, 1)[0]
+    rng = random.Random(7)
+    A = [O.random_poly(rng, 32, q) for _ in range(5)]
+    B = [O.random_poly(rng, 32, q) for _ in range(5)]
+    acc = [0] * 32
+    for a, b in zip(A, B):
+        acc = O.vec_add(acc, O.vec_mul(a, b, q), q)   # the pinned restatements of arithmetic.py:3-13
+    assert O.mul_acc(A, B, q) == acc

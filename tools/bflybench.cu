@@ -2,6 +2,7 @@
 // arithmetic (exact vs approximate high product, exact vs high-word conditional subtraction).
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o bflybench tools/bflybench.cu && ./bflybench
 #include <cstdio>
+#include <cstdlib>
 #include <cstdint>
 #include <cuda_runtime.h>
 #include "../gpu-fhe_b200/csrc/modarith.cuh"
@@ -81,6 +82,56 @@ __device__ __forceinline__ u64 dfmul_cvt(u64 x, u64 w0, u64 w1, double r0, doubl
     return r;
 }
 
+
+// ---- split representation: a residue is two 32-bit halves, each the LOW word of a register pair whose HIGH word
+// holds 0x43300000, i.e. the pair read as a double is 2^52 + half.  Integer adds write the low words directly
+// (32-bit IADD3 / IADD3.X can target any register), so the int->double conversion costs one DADD and no moves.
+struct Split { double l, h; };
+__device__ __forceinline__ Split split_make(u64 x) {
+    Split s; s.l = __hiloint2double(0x43300000, (int)(u32)x); s.h = __hiloint2double(0x43300000, (int)(u32)(x >> 32)); return s;
+}
+__device__ __forceinline__ u64 split_join(const Split& s) { return ((u64)(u32)__double2hiint(s.h) * 0 + ((u64)(u32)__double2loint(s.h) << 32)) | (u32)__double2loint(s.l); }
+// T = y*w - h*q (+K) from the split y; returns 64-bit integer
+template <bool NOFP = false>
+__device__ __forceinline__ u64 dfmul_split(const Split& y, u64 w0, u64 w1, double r0, double r1, u64 nq) {
+    u32 hlo, hhi;
+    if (NOFP) { hlo = (u32)__double2loint(y.l) ^ (u32)__double2loint(y.h); hhi = 0x43300001u; }
+    else {
+    const double ul = y.l - 4503599627370496.0, uh = y.h - 4503599627370496.0;
+    const double R = fma(ul, r0, fma(uh, r1, 4503599627370496.0));
+    hlo = (u32)__double2loint(R); hhi = (u32)__double2hiint(R); }
+    const u32 yl = (u32)__double2loint(y.l), yh = (u32)__double2loint(y.h);
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 al,ah,bl,bh,nl,nh,top,lo;\n\t"
+        ".reg .u64 acc;\n\t"
+        "mov.b64 {al,ah}, %3;\n\t"
+        "mov.b64 {bl,bh}, %4;\n\t"
+        "mov.b64 {nl,nh}, %5;\n\t"
+        "mul.wide.u32 acc, %1, al;\n\t"
+        "mad.wide.u32 acc, %2, bl, acc;\n\t"
+        "mad.wide.u32 acc, %6, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, %1, ah, top;\n\t"
+        "mad.lo.u32 top, %2, bh, top;\n\t"
+        "mad.lo.u32 top, %6, nh, top;\n\t"
+        "mad.lo.u32 top, %7, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n" : "=l"(r) : "r"(yl), "r"(yh), "l"(w0), "l"(w1), "l"(nq), "r"(hlo), "r"(hhi));
+    return r;
+}
+// s = (a op b) + c on split halves, three-input 64-bit add with the result written into the low words of s's pairs
+__device__ __forceinline__ void split_add3(Split& s, u32 al, u32 ah, u64 t, u64 c, bool sub) {
+    u32 lo, hi;
+    const u32 tl = (u32)t, th = (u32)(t >> 32), cl = (u32)c, ch = (u32)(c >> 32);
+    if (!sub) asm("{.reg .u32 x; add.cc.u32 x, %2, %4; addc.cc.u32 %1, %3, %5; add.cc.u32 %0, x, %6; addc.u32 %1, %1, %7;}"
+                  : "=r"(lo), "=&r"(hi) : "r"(al), "r"(ah), "r"(tl), "r"(th), "r"(cl), "r"(ch));
+    else asm("{.reg .u32 x; sub.cc.u32 x, %2, %4; subc.cc.u32 %1, %3, %5; add.cc.u32 %0, x, %6; addc.u32 %1, %1, %7;}"
+             : "=r"(lo), "=&r"(hi) : "r"(al), "r"(ah), "r"(tl), "r"(th), "r"(cl), "r"(ch));
+    s.l = __hiloint2double(__double2hiint(s.l), (int)lo);
+    s.h = __hiloint2double(__double2hiint(s.h), (int)hi);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u64 w, u64 ws) {
     u64 X[CH], Y[CH];
@@ -88,6 +139,10 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
     const double r0 = (double)w / (double)q, r1 = (double)ws / 18446744073709551616.0;
 #pragma unroll
     for (int i = 0; i < CH; ++i) { X[i] = (threadIdx.x * 1315423911ull + i) % q; Y[i] = (threadIdx.x * 2654435761ull + 7 * i) % q; }
+    constexpr int SC = (MODE >= 20) ? 4 : 1;   // split chains (4 registers per residue)
+    Split SX[SC], SY[SC];
+#pragma unroll
+    for (int i = 0; i < SC; ++i) { SX[i] = split_make(X[i]); SY[i] = split_make(Y[i]); }
     __syncthreads();
     u64 g0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0));
     long long t0 = clock64();
@@ -95,6 +150,16 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
     for (int it = 0; it < ITERS; ++it) {
 #pragma unroll
         for (int i = 0; i < CH; ++i) {
+            if (MODE >= 20) {   // FP64-assisted on the split representation (no moves), 21: csub every 2nd, 22: integer part only
+                if (i >= SC) continue;
+                const u64 t = dfmul_split<MODE == 22>(SY[i], w, ws, r0, r1, nq);
+                u32 xl = (u32)__double2loint(SX[i].l), xh = (u32)__double2loint(SX[i].h);
+                if (MODE == 21 && (i & 1)) {
+                    const u64 x = csub(((u64)xh << 32) | xl, q4 + q4); xl = (u32)x; xh = (u32)(x >> 32);
+                }
+                split_add3(SX[i], xl, xh, t, q2, false);
+                split_add3(SY[i], xl, xh, t, q4, true);
+            } else
             if (MODE == 0) {          // current: exact shoup, exact csub, [0,4q)
                 const u64 x = csub(X[i], q2), t = shoup_mul(Y[i], w, ws, nq);
                 X[i] = x + t; Y[i] = x - t + q2;
@@ -150,7 +215,7 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
     u64 g1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
     u64 acc = 0;
 #pragma unroll
-    for (int i = 0; i < CH; ++i) acc += X[i] ^ Y[i];
+    for (int i = 0; i < CH; ++i) acc += X[i] ^ Y[i] ^ split_join(SX[i % SC]) ^ split_join(SY[i % SC]);
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
     if (threadIdx.x == 0) { cyc[blockIdx.x] = t1 - t0; cyc[gridDim.x + blockIdx.x] = (long long)(g1 - g0); }
 }
@@ -173,7 +238,7 @@ static void run(const char* name, int sms, int threads = 512) {
     cudaMemcpy(h, cyc, sizeof(long long) * blocks * 2, cudaMemcpyDeviceToHost);
     double mean = 0, ns = 0; for (int i = 0; i < blocks; ++i) { mean += h[i]; ns += h[blocks + i]; } mean /= blocks; ns /= blocks;
     const double mhz = mean / ns * 1e3;
-    const double nb = (double)blocks * threads * ITERS * CH;          // thread-butterflies
+    const double nb = (double)blocks * threads * ITERS * (MODE >= 20 ? 4 : CH);          // thread-butterflies
     const double per_s = nb / (ms * 1e-3);
     // whole-kernel figure: warp-butterflies per SMSP = nb/32/(sms*4); clocks at 1.965 GHz
     const double clk_ev = (ms * 1e-3 * 1.965e9) / (nb / 32 / (sms * 4.0));
@@ -182,8 +247,18 @@ static void run(const char* name, int sms, int threads = 512) {
     delete[] h; cudaFree(out); cudaFree(cyc);
 }
 
-int main() {
+int main(int argc, char** argv) {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    if (argc > 1) {   // single mode, for ncu
+        const int m = atoi(argv[1]);
+        if (m == 12) run<12>("approx shoup csub/2", sms);
+        if (m == 20) run<20>("split no csub", sms);
+        if (m == 21) run<21>("split csub/2", sms);
+        if (m == 22) run<22>("split, integer part only", sms);
+        if (m == 9) run<9>("fp64 no csub", sms);
+        if (m == 3) run<3>("approx shoup no csub", sms);
+        return 0;
+    }
     run<0>("fwd  exact shoup + exact csub (current)", sms);
     run<0>("  same, 4 warps/SMSP (2 x 256 thr/SM)", sms, 256);
     run<0>("  same, 2 warps/SMSP (2 x 128 thr/SM)", sms, 128);
@@ -200,6 +275,10 @@ int main() {
     run<12>("fwd  approx shoup, csub every 2nd", sms);
     run<13>("fwd  FP64-assisted (I2F), no csub", sms);
     run<14>("fwd  FP64-assisted (I2F), csub every 2nd", sms);
+    run<20>("fwd  FP64 split-representation, no csub", sms);
+    run<21>("fwd  FP64 split-representation, csub/2", sms);
+    run<20>("  same no csub, 4 warps/SMSP", sms, 256);
+    run<22>("fwd  split, integer part only (fake quotient)", sms);
     run<7>("shoup_a alone (+1 add)", sms);
     run<8>("barrett_mul (+2 csub)", sms);
     return 0;

@@ -1,7 +1,9 @@
 // extern "C" boundary (include/gpufhe_b200.h): argument checking, error mapping, and the
 // host-buffer entry points that pipeline H2D -> kernels -> D2H over limb groups.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "../../include/gpufhe_b200.h"
 #include "plan.h"
 
@@ -244,19 +246,30 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     DeviceGuard g(pl->device);
     const size_t limb_bytes = ((size_t)batch * sizeof(u64)) << pl->logN;
     // limb groups of ~32 MiB per operand: large enough for full PCIe rate, small enough to overlap
-    u32 gl = (u32)((((size_t)32 << 20) + limb_bytes - 1) / limb_bytes);
+    size_t group_mib = 32;
+    if (const char* env = std::getenv("GFHE_HOST_GROUP_MIB")) { const long v = std::atol(env); if (v >= 1 && v <= 4096) group_mib = (size_t)v; }
+    u32 gl = (u32)(((group_mib << 20) + limb_bytes - 1) / limb_bytes);
     if (gl < 1) gl = 1;
     if (gl > pl->L) gl = pl->L;
     HostPipe* hp = nullptr;
     cudaError_t e = host_pipe_get(pl, limb_bytes * gl, &hp);
     if (e) return (int)e;
     const size_t limb_elems = (size_t)batch << pl->logN;
+    // group schedule: full groups, then a halving tail (gl/2, gl/4, ..., 1) so that what is left after the last H2D
+    // copy -- the last group's kernels and its D2H copy -- is one limb's worth, not a full group's
+    std::vector<u32> groups;
+    {
+        u32 left = pl->L;
+        while (left > gl) { groups.push_back(gl); left -= gl; }
+        for (u32 g = left; left > 0;) { g = g > 1 ? (g + 1) / 2 : 1; if (g > left) g = left; groups.push_back(g); left -= g; }
+    }
     int slot = 0;
-    for (u32 l0 = 0; l0 < pl->L; l0 += gl, slot ^= 1) {
-        const u32 nl = l0 + gl <= pl->L ? gl : pl->L - l0;
+    u32 l0 = 0;
+    for (size_t it = 0; it < groups.size(); l0 += groups[it], ++it, slot ^= 1) {
+        const u32 nl = groups[it];
         const size_t bytes = limb_bytes * nl, off = limb_elems * l0;
         u64 *da = hp->buf[slot][0], *db = hp->buf[slot][1], *dc = hp->buf[slot][2], *dw = hp->buf[slot][3];
-        if (l0 >= 2 * gl) {   // slot reuse: inputs may be overwritten once its kernels ran, output once copied out
+        if (it >= 2) {   // slot reuse: inputs may be overwritten once its kernels ran, output once copied out
             if ((e = cudaStreamWaitEvent(hp->s_in, hp->run_done[slot], 0))) return (int)e;
             if ((e = cudaStreamWaitEvent(hp->s_run, hp->out_done[slot], 0))) return (int)e;
         }

@@ -439,3 +439,21 @@ def test_automorphism_both_domains(cuda_device, logn):
         assert got == O.automorphism_ntt(X, 5)
     with pytest.raises(ValueError):
         P.automorphism(ta, 4, MOD=moduli)
+
+
+def test_poly_mul_pair_is_the_tensor_product(cuda_device):
+    import polynomial as P
+    N, L, B = 4096, 2, 2
+    moduli = O.ntt_primes(50, L)
+    xs = [dev_i64(rand_lbn(40 + i, moduli, B, N), cuda_device) for i in range(4)]
+    M = col(moduli)
+    with P.ring(moduli):
+        c0, c1, c2 = P.poly_mul_pair((xs[0], xs[1]), (xs[2], xs[3]))
+        assert torch.equal(c0, P.poly_mul(xs[0], xs[2]))
+        assert torch.equal(c2, P.poly_mul(xs[1], xs[3]))
+        assert torch.equal(c1, P.vec_add(P.poly_mul(xs[0], xs[3]), P.poly_mul(xs[1], xs[2]), M))
+    # one limb-polynomial of c1 against the schoolbook oracle
+    q = moduli[0]
+    a0, a1, b0, b1 = (host_u64(x)[0, 0].tolist() for x in xs)
+    want = O.vec_add(O.kronecker_negacyclic(a0, b1, q), O.kronecker_negacyclic(a1, b0, q), q)
+    assert host_u64(c1)[0, 0].tolist() == want

@@ -81,6 +81,9 @@ __device__ __forceinline__ u64 csub(u64 x, u64 c) {
     return (long long)d < 0 ? x : d;
 }
 
+// 32-bit form: min(x, x - c) as unsigned -- x - c wraps above x exactly when x < c.  IADD3 + VIMNMX.
+__device__ __forceinline__ u32 csub(u32 x, u32 c) { return min(x, x - c); }
+
 __device__ __forceinline__ u64 mulhi64(u64 a, u64 b) { return __umul64hi(a, b); }
 
 // Full reduction of an arbitrary 64-bit value to [0, q) with the one-word Barrett constant.
@@ -177,21 +180,43 @@ __device__ __forceinline__ u64 barrett_lazy(u64 a, u64 b, u64 nq, u64 mu, u32 s)
     return z0 + mulhi_a(x, mu) * nq;
 }
 
+// 32-bit Shoup product for moduli below 2^30: x*w - floor(x*ws32/2^32)*q in [0, 2q) for ANY 32-bit x, with
+// w < q and ws32 = floor(w*2^32/q) -- the high word of the 64-bit companion the tables already hold.
+// IMAD.HI + 2 IMAD (the 64-bit product needs 9 multiply instructions).
+__device__ __forceinline__ u32 shoup32(u32 x, u32 w, u32 ws32, u32 nq) {
+    const u32 h = __umulhi(x, ws32);
+    return x * w + h * nq;
+}
+
 // Arithmetic policies of the butterfly code (ntt_core.cuh).
-//   Harvey : exact Shoup, any q < 2^62.  forward residues in [0,4q), inverse in [0,2q).
-//   Lazy60 : approximate Shoup, 2^19 <= q < 2^60.  forward residues in [0,16q) with one conditional
-//            subtraction of 8q every second stage, inverse residues in [0,8q).
+//   Harvey  : exact Shoup, any q < 2^62.  forward residues in [0,4q), inverse in [0,2q).
+//   Lazy60  : approximate Shoup, 2^19 <= q < 2^60.  forward residues in [0,16q) with one conditional
+//             subtraction of 8q every second stage, inverse residues in [0,8q).
+//   Shoup32 : q < 2^30.  Harvey's ranges on 32-bit registers: residues are still stored as 64-bit words in HBM
+//             (the API's layout), but every butterfly is 3 multiply + 4 add/min instructions instead of 9 + 11.
 struct Harvey {
+    typedef u64 word;
     static constexpr bool kLazy = false;
     static constexpr int kFwdC = 2;   // forward offset/csub constant = kFwdC * q
     static constexpr int kInvC = 2;
     __device__ static __forceinline__ u64 mul(u64 x, u64 w, u64 ws, u64 nq) { return shoup_mul(x, w, ws, nq); }
+    __device__ static __forceinline__ u64 mul_exact(u64 x, u64 w, u64 ws, u64 nq) { return shoup_mul(x, w, ws, nq); }
 };
 struct Lazy60 {
+    typedef u64 word;
     static constexpr bool kLazy = true;
     static constexpr int kFwdC = 4;   // T < 4q
     static constexpr int kInvC = 8;
     __device__ static __forceinline__ u64 mul(u64 x, u64 w, u64 ws, u64 nq) { return shoup_a(x, w, ws, nq); }
+    __device__ static __forceinline__ u64 mul_exact(u64 x, u64 w, u64 ws, u64 nq) { return shoup_mul(x, w, ws, nq); }
+};
+struct Shoup32 {
+    typedef u32 word;
+    static constexpr bool kLazy = false;
+    static constexpr int kFwdC = 2;
+    static constexpr int kInvC = 2;
+    __device__ static __forceinline__ u32 mul(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
+    __device__ static __forceinline__ u32 mul_exact(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
 };
 
 }  // namespace gfhe

@@ -79,7 +79,8 @@ struct TwT0 {
 // in [0,16q); the product is < 4q, so X grows by 4q per stage and is brought under 8q at the first
 // and third stage of a round (every round therefore maps [0,16q) to [0,16q)).
 template <class A, int B_HI, int B_LO, class TW>
-__device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 C, u64 nq) {
+__device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq) {
+    typedef typename A::word W;
 #pragma unroll
     for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
         const int b = B_HI - sidx;
@@ -90,8 +91,8 @@ __device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 C, 
 #pragma unroll
             for (int lo = 0; lo < (1 << b); ++lo) {
                 const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
-                const u64 X = reduce_x ? csub(r[ix], A::kLazy ? 2 * C : C) : r[ix];
-                const u64 T = A::mul(r[iy], t.x, t.y, nq);
+                const W X = reduce_x ? csub(r[ix], A::kLazy ? 2 * C : C) : r[ix];
+                const W T = A::mul(r[iy], t.x, t.y, nq);
                 r[ix] = X + T;
                 r[iy] = X - T + C;
             }
@@ -101,14 +102,14 @@ __device__ __forceinline__ void fwd_round(u64 (&r)[kElems], const TW tw, u64 C, 
 
 // Reduction of a forward residue that feeds the pointwise product: [0, 2q) is enough for Lazy60.
 template <class A>
-__device__ __forceinline__ u64 fwd_semi(u64 x, u64 q, u64 nq, u32 kshift, u32 kmu) {
+__device__ __forceinline__ typename A::word fwd_semi(typename A::word x, typename A::word q, typename A::word nq, u32 kshift, u32 kmu) {
     if constexpr (A::kLazy) return kred(x, kshift, kmu, nq);
     else return csub(csub(x, 2 * q), q);
 }
 
 // Full reduction of a forward residue to [0, q).
 template <class A>
-__device__ __forceinline__ u64 fwd_final(u64 x, u64 q, u64 nq, u32 kshift, u32 kmu) {
+__device__ __forceinline__ typename A::word fwd_final(typename A::word x, typename A::word q, typename A::word nq, u32 kshift, u32 kmu) {
     if constexpr (A::kLazy) return csub(kred(x, kshift, kmu, nq), q);   // [0,16q) -> [0,2q) -> [0,q)
     else return csub(csub(x, 2 * q), q);                                // [0,4q)
 }
@@ -118,20 +119,22 @@ __device__ __forceinline__ u64 fwd_final(u64 x, u64 q, u64 nq, u32 kshift, u32 k
 // LAST: local bit B_HI is the final stage of the whole transform; it multiplies by N^-1
 // (folded: U' = (U+V)*N^-1, V' = (U-V)*psi^-brv(1)*N^-1) with the exact product and fully reduces to [0, q).
 template <class A, int B_HI, int B_LO, bool LAST, class TW>
-__device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 C, u64 nq, const LimbParams* __restrict__ Pg) {
+__device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq,
+                                          const LimbParams* __restrict__ Pg) {
+    typedef typename A::word W;
 #pragma unroll
     for (int b = B_LO; b <= B_HI; ++b) {
         if (LAST && b == B_HI) {
             // per-limb constants of the final stage are fetched here, not held in registers all along
             const ulonglong2 cn = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->ninv));
             const ulonglong2 cw = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->w1ninv));
-            const u64 q = 0 - nq;
+            const W q = 0 - nq;
 #pragma unroll
             for (int lo = 0; lo < (1 << b); ++lo) {                  // B_HI == 3 here: one group
                 const int ix = lo, iy = ix + (1 << b);
-                const u64 U = r[ix], V = r[iy];
-                r[ix] = csub(shoup_mul(U + V, cn.x, cn.y, nq), q);
-                r[iy] = csub(shoup_mul(U - V + C, cw.x, cw.y, nq), q);
+                const W U = r[ix], V = r[iy];
+                r[ix] = csub(A::mul_exact(U + V, cn.x, cn.y, nq), q);
+                r[iy] = csub(A::mul_exact(U - V + C, cw.x, cw.y, nq), q);
             }
         } else {
 #pragma unroll
@@ -140,7 +143,7 @@ __device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 C, 
 #pragma unroll
                 for (int lo = 0; lo < (1 << b); ++lo) {
                     const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
-                    const u64 U = r[ix], V = r[iy];
+                    const W U = r[ix], V = r[iy];
                     r[ix] = csub(U + V, C);                           // [0,C)
                     r[iy] = A::mul(U - V + C, t.x, t.y, nq);          // [0,2q) or [0,4q)
                 }
@@ -150,10 +153,10 @@ __device__ __forceinline__ void inv_round(u64 (&r)[kElems], const TW tw, u64 C, 
 }
 
 // ---- shared-memory re-distribution ---------------------------------------------------------------
-template <int P0>
-__device__ __forceinline__ void sm_store(u64* sm, u32 tid, const u64 (&r)[kElems]) {
-    u64* p = sm + pad(elem_index<P0>(tid, 0));
-    if constexpr (P0 == 0) {
+template <int P0, class W>
+__device__ __forceinline__ void sm_store(W* sm, u32 tid, const W (&r)[kElems]) {
+    W* p = sm + pad(elem_index<P0>(tid, 0));
+    if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) *reinterpret_cast<ulonglong2*>(p + 2 * j) = make_ulonglong2(r[2 * j], r[2 * j + 1]);
     } else {
@@ -161,10 +164,10 @@ __device__ __forceinline__ void sm_store(u64* sm, u32 tid, const u64 (&r)[kElems
         for (int i = 0; i < kElems; ++i) p[pad((u32)i << P0)] = r[i];
     }
 }
-template <int P0>
-__device__ __forceinline__ void sm_load(const u64* sm, u32 tid, u64 (&r)[kElems]) {
-    const u64* p = sm + pad(elem_index<P0>(tid, 0));
-    if constexpr (P0 == 0) {
+template <int P0, class W>
+__device__ __forceinline__ void sm_load(const W* sm, u32 tid, W (&r)[kElems]) {
+    const W* p = sm + pad(elem_index<P0>(tid, 0));
+    if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + 2 * j);
@@ -205,7 +208,8 @@ __device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
 // (window at bit 0: 16 contiguous residues per thread).  The slab may be a tile of several independent
 // 2^LOGS-point sub-transforms (tid then spans more than 2^(LOGS-4) threads): nothing here depends on it.
 template <class A, int LOGS>
-__device__ __forceinline__ void slab_fwd(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 C, u64 nq) {
+__device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
+                                         typename A::word C, typename A::word nq) {
     using S = Sched<LOGS>;
     {
         constexpr int P0 = S::p0(0);
@@ -232,8 +236,8 @@ __device__ __forceinline__ void slab_fwd(u64 (&r)[kElems], u64* sm, u32 tid, con
 // Entry layout: window at bit 0; exit layout: window at bit p0(0).
 // LAST: the slab is the whole polynomial (N == 2^LOGS), so the top stage folds N^-1.
 template <class A, int LOGS, bool LAST>
-__device__ __forceinline__ void slab_inv(u64 (&r)[kElems], u64* sm, u32 tid, const TwTab& T, u32 off, u64 C, u64 nq,
-                                         const LimbParams* __restrict__ Pg) {
+__device__ __forceinline__ void slab_inv(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
+                                         typename A::word C, typename A::word nq, const LimbParams* __restrict__ Pg) {
     using S = Sched<LOGS>;
     if constexpr (S::NR > 2) {
         constexpr int P0 = S::p0(2), PN = S::p0(1);

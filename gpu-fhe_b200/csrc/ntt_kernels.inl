@@ -61,14 +61,15 @@ __device__ __forceinline__ TwTab limb_tables(const Tables& T, u32 limb, u32 logN
 }
 
 // Per-limb scalars every kernel needs: Cf/Ci = offset constants of the arithmetic policy.
-struct LimbK { u64 q, nq, Cf, Ci; };
+template <class W> struct LimbK { W q, nq, Cf, Ci; };
 template <class A>
-__device__ __forceinline__ LimbK limb_consts(const LimbParams* __restrict__ Pg) {
-    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->q2));   // {2q, -q}
-    return LimbK{v.x >> 1, v.y, (u64)(A::kFwdC / 2) * v.x, (u64)(A::kInvC / 2) * v.x};
+__device__ __forceinline__ LimbK<typename A::word> limb_consts(const LimbParams* __restrict__ Pg) {
+    typedef typename A::word W;
+    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->q2));   // {2q, -q mod 2^64}
+    return LimbK<W>{(W)(v.x >> 1), (W)v.y, (W)((u64)(A::kFwdC / 2) * v.x), (W)((u64)(A::kInvC / 2) * v.x)};
 }
 template <class A>
-__device__ __forceinline__ void fwd_final_all(u64 (&r)[kElems], const LimbK& K, const LimbParams* __restrict__ Pg) {
+__device__ __forceinline__ void fwd_final_all(typename A::word (&r)[kElems], const LimbK<typename A::word>& K, const LimbParams* __restrict__ Pg) {
     u32 ks = 0, km = 0;
     if constexpr (A::kLazy) { ks = __ldg(&Pg->kshift); km = (u32)__ldg(&Pg->kmu); }
 #pragma unroll
@@ -76,7 +77,7 @@ __device__ __forceinline__ void fwd_final_all(u64 (&r)[kElems], const LimbK& K, 
 }
 
 template <class A>
-__device__ __forceinline__ void fwd_semi_all(u64 (&r)[kElems], const LimbK& K, const LimbParams* __restrict__ Pg) {
+__device__ __forceinline__ void fwd_semi_all(typename A::word (&r)[kElems], const LimbK<typename A::word>& K, const LimbParams* __restrict__ Pg) {
     u32 ks = 0, km = 0;
     if constexpr (A::kLazy) { ks = __ldg(&Pg->kshift); km = (u32)__ldg(&Pg->kmu); }
 #pragma unroll
@@ -90,6 +91,29 @@ __device__ __forceinline__ void copy_out_padded(const u64* sm, u64* out, u32 tid
     for (int it = 0; it < 8; ++it) {
         const u32 e = 2u * (it * NT + tid);
         *reinterpret_cast<ulonglong2*>(out + e) = *reinterpret_cast<const ulonglong2*>(sm + pad(e));
+    }
+}
+// 32-bit words in shared memory, 64-bit words in HBM: pad(e) is even for even e, so the pair is one 8-byte access
+template <int LOGT>
+__device__ __forceinline__ void copy_out_padded(const u32* sm, u64* out, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const u32 e = 2u * (it * NT + tid);
+        const uint2 v = *reinterpret_cast<const uint2*>(sm + pad(e));
+        *reinterpret_cast<ulonglong2*>(out + e) = make_ulonglong2(v.x, v.y);
+    }
+}
+template <int LOGT>
+__device__ __forceinline__ void copy_in_padded(u32* sm, const u64* in, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        ulonglong2 v[4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it) v[it] = *reinterpret_cast<const ulonglong2*>(in + 2u * ((4 * h + it) * NT + tid));
+#pragma unroll
+        for (int it = 0; it < 4; ++it) *reinterpret_cast<uint2*>(sm + pad(2u * ((4 * h + it) * NT + tid))) = make_uint2((u32)v[it].x, (u32)v[it].y);
     }
 }
 template <int LOGT>
@@ -109,16 +133,17 @@ __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) 
 template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[padded_words(LOGT)];
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
-    const LimbK K = limb_consts<A>(Pg);
+    const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
-    u64 r[kElems];
+    W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (in + s.g0 + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = (W)(in + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     if constexpr (LOGT > 4) {
@@ -136,20 +161,21 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
-    __shared__ __align__(16) u64 sm[padded_words(LOGT)];
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
-    const LimbK K = limb_consts<A>(Pg);
+    const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
-    u64 r[kElems];
+    W r[kElems];
     if constexpr (LOGT > 4) {
         copy_in_padded<LOGT>(sm, in + s.g0, tid);
         __syncthreads();
         sm_load<0>(sm, tid, r);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = in[s.g0 + i];
+        for (int i = 0; i < kElems; ++i) r[i] = (W)in[s.g0 + i];
     }
     slab_inv<A, LOGS, WHOLE>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);
     constexpr int P0 = Sched<LOGS>::p0(0);
@@ -185,35 +211,36 @@ __device__ __forceinline__ void tma_tile_wait(u64* mbar) {
 template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
+    typedef typename A::word W;
     extern __shared__ __align__(16) u64 smem[];
-    u64* sm0 = smem;                 // exchange buffer
-    u64* sm1 = smem + padded_words(LOGT);   // stash for NTT(a) while NTT(b) is computed
-    u64* smb = sm1 + padded_words(LOGT);    // b's tile, fetched by one TMA bulk copy while a is transformed
+    W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
+    W* sm1 = reinterpret_cast<W*>(smem + padded_words(LOGT));      // stash for NTT(a) while NTT(b) is computed
+    u64* smb = smem + 2 * padded_words(LOGT);   // b's tile, fetched by one TMA bulk copy while a is transformed
     u64* mbar = smb + (1 << LOGT);
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(u64) << LOGT, mbar);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
-    const LimbK K = limb_consts<A>(Pg);
+    const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab Tf = limb_tables(tf, s.limb, logN);
     const TwTab Ti = limb_tables(ti, s.limb, logN);
     constexpr int P0 = Sched<LOGS>::p0(0);
-    u64 r[kElems];
+    W r[kElems];
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (a + s.g0 + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = (W)(a + s.g0 + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
-    sm_store<0>(sm1, tid, r);   // private 144-byte row of sm1: written and read back by this thread only
+    sm_store<0>(sm1, tid, r);   // private row of sm1: written and read back by this thread only
     __syncthreads();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
     tma_tile_wait(mbar);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (smb + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = (W)(smb + elem_index<P0>(tid, 0))[i << P0];
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
-    {
+    if constexpr (sizeof(W) == 8) {
         const u64 mu = __ldg(&Pg->bar_mu);
         const u32 bs = __ldg(&Pg->bar_shift);
-        const u64* pa = sm1 + pad(tid << 4);
+        const u64* pa = reinterpret_cast<const u64*>(sm1) + pad(tid << 4);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(pa + 2 * j);
@@ -224,6 +251,15 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
                 r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
                 r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
             }
+        }
+    } else {   // 32-bit words: a, b < q < 2^30, one-word Barrett on the 60-bit product
+        const u64 b64 = __ldg(&Pg->bar64);
+        const W* pa = sm1 + pad(tid << 4);
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) {
+            const u64 z = (u64)pa[i] * r[i];
+            const u64 qh = mulhi64(z, b64);                  // floor(z/q) - 1 <= qh <= floor(z/q)
+            r[i] = csub((W)z + (W)qh * K.nq, K.q);           // z - qh*q in [0, 2q) fits 32 bits
         }
     }
     slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
@@ -263,19 +299,20 @@ template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
 k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
-    __shared__ __align__(16) u64 sm[Geo::TWO ? padded_words(12) : 2];
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
     const u64* in = (blockIdx.y ? in1 : in0) + id.base;
     u64* out = (blockIdx.y ? out1 : out0) + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
-    const LimbK K = limb_consts<A>(Pg);
+    const LimbK<W> K = limb_consts<A>(Pg);
     __shared__ ulonglong2 tws[256];
-    u64 r[kElems];
+    W r[kElems];
     {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<8>(i)];
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
     __syncthreads();
@@ -299,23 +336,24 @@ template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, 2)
 k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
-    __shared__ __align__(16) u64 sm[Geo::TWO ? padded_words(12) : 2];
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
     const u64* in = in0 + id.base;
     u64* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
-    const LimbK K = limb_consts<A>(Pg);
+    const LimbK<W> K = limb_consts<A>(Pg);
     __shared__ ulonglong2 tws[256];
-    u64 r[kElems];
+    W r[kElems];
     if constexpr (Geo::TWO) {
         const u64* p = in + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<4>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<4>(i)];
     } else {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = p[Geo::template roff<8>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<8>(i)];
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);
     __syncthreads();

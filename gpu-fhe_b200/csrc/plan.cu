@@ -105,7 +105,9 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     pl->lazy = true;
     for (u32 l = 0; l < L; ++l) { const u32 k = 64 - (u32)__builtin_clzll(moduli[l]); if (k > pl->max_bits) pl->max_bits = k; }
     for (u32 l = 0; l < L; ++l) if (moduli[l] < (1ull << 19) || moduli[l] >= (1ull << 60)) pl->lazy = false;
-    if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->lazy = false;
+    pl->w32 = pl->max_bits <= 30;
+    if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') { pl->lazy = false; pl->w32 = false; }
+    if (const char* env = std::getenv("GFHE_NO_W32")) if (env[0] == '1') pl->w32 = false;
 
     std::vector<LimbParams> hp(L);
     for (u32 l = 0; l < L; ++l) fill_limb_params(hp[l], moduli[l], logN, logN ? psi[l] : 0);
@@ -151,14 +153,18 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
 // ---- policy dispatch ---------------------------------------------------------------------------
 extern template struct Launcher<Harvey>;
 extern template struct Launcher<Lazy60>;
+extern template struct Launcher<Shoup32>;
 
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    if (pl.w32) return Launcher<Shoup32>::ntt_fwd(pl, limb0, nl, in, out, B, st);
     return pl.lazy ? Launcher<Lazy60>::ntt_fwd(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_fwd(pl, limb0, nl, in, out, B, st);
 }
 cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    if (pl.w32) return Launcher<Shoup32>::ntt_inv(pl, limb0, nl, in, out, B, st);
     return pl.lazy ? Launcher<Lazy60>::ntt_inv(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_inv(pl, limb0, nl, in, out, B, st);
 }
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
+    if (pl.w32) return Launcher<Shoup32>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st)
                    : Launcher<Harvey>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
 }

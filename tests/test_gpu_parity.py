@@ -457,3 +457,36 @@ def test_poly_mul_pair_is_the_tensor_product(cuda_device):
     a0, a1, b0, b1 = (host_u64(x)[0, 0].tolist() for x in xs)
     want = O.vec_add(O.kronecker_negacyclic(a0, b1, q), O.kronecker_negacyclic(a1, b0, q), q)
     assert host_u64(c1)[0, 0].tolist() == want
+
+
+# ---------------------------------------------------------------------------------------------------
+# 32-bit arithmetic policy (moduli below 2^30): every kernel instantiation against the C oracle, and
+# bit-identical to the 64-bit kernels on the same inputs
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logn", [4, 5, 8, 10, 12, 13, 14, 16, 17, 18])
+def test_w32_policy_all_sizes(cuda_device, logn, monkeypatch):
+    import polynomial as P
+    N = 1 << logn
+    moduli = P.ntt_primes(30, 2, N=max(N, 1 << 12))
+    assert all(q < (1 << 30) for q in moduli)
+    B = 3 if logn <= 16 else 1
+    a, b = rand_lbn(100 + logn, moduli, B, N), rand_lbn(200 + logn, moduli, B, N)
+    a[:, 0, :4] = np.array(moduli, dtype=np.uint64).reshape(2, 1) - 1      # extremes: q-1 and 0
+    b[:, 0, :4] = np.array(moduli, dtype=np.uint64).reshape(2, 1) - 1
+    a[:, 0, 4] = 0
+    R = oracle_ring(N, moduli)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    P.clear_plans()
+    with P.ring(moduli):
+        X, c = P.NTT(ta), P.poly_mul(ta, tb)
+        back = P.iNTT(X)
+    assert np.array_equal(host_u64(X), R.ntt(a, fast=True, nthreads=4))
+    assert torch.equal(back, ta)
+    assert np.array_equal(host_u64(c), R.poly_mul(a, b, fast=True, nthreads=4))
+    # the same plan forced onto the 64-bit kernels gives identical words
+    monkeypatch.setenv("GFHE_NO_W32", "1")
+    P.clear_plans()
+    with P.ring(moduli):
+        assert torch.equal(P.NTT(ta), X) and torch.equal(P.poly_mul(ta, tb), c)
+    monkeypatch.delenv("GFHE_NO_W32")
+    P.clear_plans()

@@ -43,6 +43,10 @@ __device__ __forceinline__ u32 elem_index(u32 tid, u32 i) {
 // depends only on addresses, so the compiler hoists the loads of later transforms of a fused kernel to the
 // top and then spills them.
 __device__ __forceinline__ ulonglong2 ldg_tw(const ulonglong2* p) {
+#ifdef GFHE_EXP_NOTW   // timing experiment only: no twiddle load (results are garbage)
+    const u64 a = (u64)(uintptr_t)p;
+    return make_ulonglong2(a | 1, a ^ 0x9E3779B97F4A7C15ull);
+#endif
     ulonglong2 v;
     asm volatile("ld.global.nc.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     return v;

@@ -220,6 +220,55 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
     if (threadIdx.x == 0) { cyc[blockIdx.x] = t1 - t0; cyc[gridDim.x + blockIdx.x] = (long long)(g1 - g0); }
 }
 
+
+// ---- FP64 butterfly for moduli below 2^50 (error-free product: h = y*w rounded, l = fma(y,w,-h) exact) ----------
+template <int RED>
+__global__ void __launch_bounds__(512, 2) kf(double* out, double q, double w, double wq) {
+    double X[CH], Y[CH];
+    const double M = 6755399441055744.0;   // 1.5 * 2^52: fma(y, wq, M) - M = rint(y * wq)
+    const double qi = 1.0 / q;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) { X[i] = (double)((threadIdx.x * 1315423911ull + i) % (1ull << 49)); Y[i] = (double)((threadIdx.x * 2654435761ull + 7 * i) % (1ull << 49)); }
+#pragma unroll 1
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+            const double y = Y[i];
+            const double c = fma(y, wq, M) - M;
+            const double h = y * w;
+            const double l = fma(y, w, -h);
+            const double d = fma(-c, q, h);
+            const double T = d + l;
+            double x = X[i];
+            if (RED && (i & 3) == (it & 3)) x = fma(-(fma(x, qi, M) - M), q, x);   // one full reduction per 4 butterflies
+            X[i] = x + T; Y[i] = x - T;
+        }
+    }
+    double acc = 0;
+#pragma unroll
+    for (int i = 0; i < CH; ++i) acc += X[i] + Y[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+template <int RED>
+static void runf(const char* name, int sms, int threads = 512) {
+    double* out;
+    const int blocks = sms * 2 * 8;
+    cudaMalloc(&out, sizeof(double) * blocks * 512);
+    const double q = 1125899902124033.0, w = 93790016731446.0;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    kf<RED><<<blocks, threads>>>(out, q, w, w / q);
+    cudaEventRecord(e0);
+    kf<RED><<<blocks, threads>>>(out, q, w, w / q);
+    cudaEventRecord(e1);
+    cudaDeviceSynchronize();
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    const double nb = (double)blocks * threads * ITERS * CH;
+    const double clk_ev = (ms * 1e-3 * 1.965e9) / (nb / 32 / (sms * 4.0));
+    printf("%-42s %6.2f Tbfly/s   %6.2f clk/warp-bfly/SMSP (events @1.965GHz)  err=%s\n", name, nb / (ms * 1e-3) * 1e-12, clk_ev,
+           cudaGetErrorString(cudaGetLastError()));
+    cudaFree(out);
+}
+
 template <int MODE>
 static void run(const char* name, int sms, int threads = 512) {
     const u64 q = 1152921504606584833ull, w = 987813353222176621ull;
@@ -279,6 +328,9 @@ int main(int argc, char** argv) {
     run<21>("fwd  FP64 split-representation, csub/2", sms);
     run<20>("  same no csub, 4 warps/SMSP", sms, 256);
     run<22>("fwd  split, integer part only (fake quotient)", sms);
+    runf<0>("FP64 butterfly q<2^50, no range reduction", sms);
+    runf<1>("FP64 butterfly q<2^50, reduce 1 in 4", sms);
+    runf<1>("  same, 4 warps/SMSP", sms, 256);
     run<7>("shoup_a alone (+1 add)", sms);
     run<8>("barrett_mul (+2 csub)", sms);
     return 0;

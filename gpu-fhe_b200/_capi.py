@@ -10,7 +10,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpufhe_b200.so")
+LIB_PATH = os.environ.get("GFHE_B200_LIB") or os.path.join(_HERE, "libgpufhe_b200.so")   # override: timing experiments only
 
 u64p = ctypes.POINTER(ctypes.c_uint64)
 i64p = ctypes.POINTER(ctypes.c_int64)

@@ -17,6 +17,19 @@
 #pragma once
 #include "modarith.cuh"
 
+// timing experiments only (results are garbage when set): -DGFHE_EXP_NOSYNC drops the CTA barriers of the exchanges,
+// -DGFHE_EXP_NOGLD replaces the global loads of residues by register arithmetic
+#ifdef GFHE_EXP_NOSYNC
+#define GFHE_SYNC() __syncwarp()
+#else
+#define GFHE_SYNC() __syncthreads()
+#endif
+#ifdef GFHE_EXP_NOGLD
+#define GFHE_GLD(T, expr, fake) ((T)(fake))
+#else
+#define GFHE_GLD(T, expr, fake) ((T)(expr))
+#endif
+
 namespace gfhe {
 
 constexpr int kElems = 16;       // residues per thread
@@ -222,7 +235,7 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
     if constexpr (S::NR > 1) {
         constexpr int PP = S::p0(0), P0 = S::p0(1);
         sm_store<PP>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
         fwd_round<A, S::top(1) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
     }
@@ -230,7 +243,7 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
         constexpr int PP = S::p0(1), P0 = S::p0(2);
         // no barrier needed: every thread overwrites exactly the words it read in the previous exchange
         sm_store<PP>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
         fwd_round<A, S::top(2) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
     }
@@ -247,14 +260,14 @@ __device__ __forceinline__ void slab_inv(typename A::word (&r)[kElems], typename
         constexpr int P0 = S::p0(2), PN = S::p0(1);
         inv_round<A, S::top(2) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<PN>(sm, tid, r);
     }
     if constexpr (S::NR > 1) {
         constexpr int P0 = S::p0(1), PN = S::p0(0);
         inv_round<A, S::top(1) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<PN>(sm, tid, r);
     }
     {

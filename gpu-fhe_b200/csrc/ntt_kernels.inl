@@ -143,12 +143,12 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (W)(in + s.g0 + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     if constexpr (LOGT > 4) {
         sm_store<0>(sm, tid, r);   // own 128-byte row: no hazard with the preceding sm_load<0>
-        __syncthreads();
+        GFHE_SYNC();
         copy_out_padded<LOGT>(sm, out + s.g0, tid);
     } else {
 #pragma unroll
@@ -171,7 +171,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     W r[kElems];
     if constexpr (LOGT > 4) {
         copy_in_padded<LOGT>(sm, in + s.g0, tid);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<0>(sm, tid, r);
     } else {
 #pragma unroll
@@ -227,11 +227,11 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     constexpr int P0 = Sched<LOGS>::p0(0);
     W r[kElems];
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (W)(a + s.g0 + elem_index<P0>(tid, 0))[i << P0];
+    for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
     sm_store<0>(sm1, tid, r);   // private row of sm1: written and read back by this thread only
-    __syncthreads();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
+    GFHE_SYNC();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
     tma_tile_wait(mbar);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = (W)(smb + elem_index<P0>(tid, 0))[i << P0];
@@ -312,14 +312,14 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
     {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<8>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
-    __syncthreads();
+    GFHE_SYNC();
     fwd_round<A, 3, Geo::LO8>(r, TwSm{tws, 1u}, K.Cf, K.nq);
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<4>(sm, tid, r);
         fwd_round<A, 3, Geo::LO4>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         u64* p = out + Geo::template toff<4>(tid);
@@ -349,18 +349,18 @@ k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     if constexpr (Geo::TWO) {
         const u64* p = in + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<4>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<4>(i)], tid * 77u + i);
     } else {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = (W)p[Geo::template roff<8>(i)];
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);
-    __syncthreads();
+    GFHE_SYNC();
     if constexpr (Geo::TWO) {
         inv_round<A, 3, Geo::LO4, false>(r, TwSm{tws, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
         sm_store<4>(sm, tid, r);
-        __syncthreads();
+        GFHE_SYNC();
         sm_load<8>(sm, tid, r);
     }
     inv_round<A, 3, Geo::LO8, true>(r, TwSm{tws, 1u}, K.Ci, K.nq, Pg);

@@ -131,6 +131,11 @@ __device__ __forceinline__ typename A::word fwd_final(typename A::word x, typena
     else return csub(csub(x, 2 * q), q);                                // [0,4q)
 }
 
+// Static range tracking of the lazy inverse round: after a stage on local bit b-1, the registers with that bit set hold
+// fresh products (< 4q) and the others sums (< 8q); the pair (ix, iy) of the next stage differs in bit b only, so both
+// of its inputs are of the same kind.  A pair of products needs no conditional subtraction (12 of the 32 in a round).
+__host__ __device__ constexpr bool inv_pair_is_fresh(int b, int b_lo, int lo) { return b > b_lo && ((lo >> (b - 1)) & 1) != 0; }
+
 // ---- one round of inverse (GS) stages on local bits B_LO..B_HI --------------------------------
 // C = A::kInvC * q: residues stay in [0, C) (Harvey 2q, Lazy60 8q).
 // LAST: local bit B_HI is the final stage of the whole transform; it multiplies by N^-1
@@ -161,8 +166,14 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
                 for (int lo = 0; lo < (1 << b); ++lo) {
                     const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
                     const W U = r[ix], V = r[iy];
-                    r[ix] = csub(U + V, C);                           // [0,C)
-                    r[iy] = A::mul(U - V + C, t.x, t.y, nq);          // [0,2q) or [0,4q)
+                    if (A::kLazy && inv_pair_is_fresh(b, B_LO, lo)) {
+                        // both inputs are products of the previous stage, < 4q: the sum is < 8q as it stands
+                        r[ix] = U + V;
+                        r[iy] = A::mul(U - V + (C >> 1), t.x, t.y, nq);
+                    } else {
+                        r[ix] = csub(U + V, C);                           // [0,C)
+                        r[iy] = A::mul(U - V + C, t.x, t.y, nq);          // [0,2q) or [0,4q)
+                    }
                 }
             }
         }

@@ -31,6 +31,7 @@ SYMBOLS = {
     "gfhe_vec_add": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_sub": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_mul": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_poly_mul_pre": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
     "gfhe_ntt_mul_acc": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, u32, vp, vp, ctypes.c_uint64, vp, vp]),
     "gfhe_automorphism": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),

@@ -142,6 +142,16 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
                                 S(stream));
 }
 
+int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                      const uint64_t* d_a, const uint64_t* d_b_ntt, uint64_t* d_c, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (!d_a || !d_b_ntt || !d_c || batch == 0) return GFHE_EARG;
+    if (P(plan)->logN == 0) return GFHE_ENOTABLES;
+    if (d_c == d_a || d_c == d_b_ntt) return GFHE_EARG;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_poly_mul_pre(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b_ntt, (u64*)d_c, batch, S(stream));
+}
+
 int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner, uint32_t terms,
                      const uint64_t* d_a, const uint64_t* d_b, uint64_t term_stride, uint64_t* d_out, void* stream) {
     if (int rc = check_range(P(plan), limb0, nl)) return rc;

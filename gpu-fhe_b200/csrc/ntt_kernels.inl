@@ -212,7 +212,9 @@ __device__ __forceinline__ void tma_tile_wait(u64* mbar) {
 
 // Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
 // is the complete negacyclic product of one limb-polynomial in a single launch.
-template <class A, int LOGS, int LOGT, bool WHOLE>
+// BNTT: b is already in the NTT domain (canonical residues, the order gfhe_ntt_forward writes): its forward transform is
+// skipped and NTT(a) never leaves the registers -- a third of the butterflies gone for callers that cache NTT(b).
+template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
 k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
     typedef typename A::word W;
@@ -234,36 +236,65 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
-    sm_store<0>(sm1, tid, r);   // private row of sm1: written and read back by this thread only
-    GFHE_SYNC();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
-    tma_tile_wait(mbar);
+    if constexpr (BNTT) {
+        tma_tile_wait(mbar);
+        const u64* pb = smb + (tid << 4);   // this thread's 16 residues of NTT(b), same positions as r[]
+        if constexpr (sizeof(W) == 8) {
+            const u64 mu = __ldg(&Pg->bar_mu);
+            const u32 bs = __ldg(&Pg->bar_shift);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = (W)(smb + elem_index<P0>(tid, 0))[i << P0];
-    slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
-    fwd_semi_all<A>(r, K, Pg);
-    if constexpr (sizeof(W) == 8) {
-        const u64 mu = __ldg(&Pg->bar_mu);
-        const u32 bs = __ldg(&Pg->bar_shift);
-        const u64* pa = reinterpret_cast<const u64*>(sm1) + pad(tid << 4);
+            for (int j = 0; j < 8; ++j) {
+                const ulonglong2 vb = *reinterpret_cast<const ulonglong2*>(pb + 2 * j);
+                if constexpr (A::kLazy) {
+                    r[2 * j] = barrett_lazy(r[2 * j], vb.x, K.nq, mu, bs);
+                    r[2 * j + 1] = barrett_lazy(r[2 * j + 1], vb.y, K.nq, mu, bs);
+                } else {
+                    r[2 * j] = barrett_mul(r[2 * j], vb.x, K.q, mu, bs);
+                    r[2 * j + 1] = barrett_mul(r[2 * j + 1], vb.y, K.q, mu, bs);
+                }
+            }
+        } else {
+            const u64 b64 = __ldg(&Pg->bar64);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(pa + 2 * j);
-            if constexpr (A::kLazy) {
-                r[2 * j] = barrett_lazy(va.x, r[2 * j], K.nq, mu, bs);
-                r[2 * j + 1] = barrett_lazy(va.y, r[2 * j + 1], K.nq, mu, bs);
-            } else {
-                r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
-                r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
+            for (int i = 0; i < kElems; ++i) {
+                const u64 z = (u64)r[i] * (W)pb[i];
+                const u64 qh = mulhi64(z, b64);
+                r[i] = csub((W)z + (W)qh * K.nq, K.q);
             }
         }
-    } else {   // 32-bit words: a, b < q < 2^30, one-word Barrett on the 60-bit product
-        const u64 b64 = __ldg(&Pg->bar64);
-        const W* pa = sm1 + pad(tid << 4);
-#pragma unroll
-        for (int i = 0; i < kElems; ++i) {
-            const u64 z = (u64)pa[i] * r[i];
-            const u64 qh = mulhi64(z, b64);                  // floor(z/q) - 1 <= qh <= floor(z/q)
-            r[i] = csub((W)z + (W)qh * K.nq, K.q);           // z - qh*q in [0, 2q) fits 32 bits
+        GFHE_SYNC();   // the exchange buffer is reused by the inverse transform
+    } else {
+        sm_store<0>(sm1, tid, r);   // private row of sm1: written and read back by this thread only
+        GFHE_SYNC();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
+        tma_tile_wait(mbar);
+    #pragma unroll
+        for (int i = 0; i < kElems; ++i) r[i] = (W)(smb + elem_index<P0>(tid, 0))[i << P0];
+        slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
+        fwd_semi_all<A>(r, K, Pg);
+        if constexpr (sizeof(W) == 8) {
+            const u64 mu = __ldg(&Pg->bar_mu);
+            const u32 bs = __ldg(&Pg->bar_shift);
+            const u64* pa = reinterpret_cast<const u64*>(sm1) + pad(tid << 4);
+    #pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(pa + 2 * j);
+                if constexpr (A::kLazy) {
+                    r[2 * j] = barrett_lazy(va.x, r[2 * j], K.nq, mu, bs);
+                    r[2 * j + 1] = barrett_lazy(va.y, r[2 * j + 1], K.nq, mu, bs);
+                } else {
+                    r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
+                    r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
+                }
+            }
+        } else {   // 32-bit words: a, b < q < 2^30, one-word Barrett on the 60-bit product
+            const u64 b64 = __ldg(&Pg->bar64);
+            const W* pa = sm1 + pad(tid << 4);
+    #pragma unroll
+            for (int i = 0; i < kElems; ++i) {
+                const u64 z = (u64)pa[i] * r[i];
+                const u64 qh = mulhi64(z, b64);                  // floor(z/q) - 1 <= qh <= floor(z/q)
+                r[i] = csub((W)z + (W)qh * K.nq, K.q);           // z - qh*q in [0, 2q) fits 32 bits
+            }
         }
     }
     slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
@@ -393,18 +424,18 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
     return (unsigned)(((u64)nl * B) << (pl.logN - logT));
 }
 
-template <class A, int LOGS, int LOGT, bool WHOLE>
+template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
     const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<A, LOGS, LOGT, WHOLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_row_polymul<A, LOGS, LOGT, WHOLE, BNTT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured[dev] = true;
     }
-    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<A, LOGS, LOGT, WHOLE><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
+    { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<A, LOGS, LOGT, WHOLE, BNTT><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
     return cudaGetLastError();
 }
 
@@ -495,6 +526,27 @@ cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* 
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, b, ws, B, nt, st)) return e;
     cudaError_t e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
                                              : launch_row_polymul<A, 12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
+    if (e != cudaSuccess) return e;
+    if ((e = launch_col_inv<A>(pl, limb0, c, c, B, nt, st)) != cudaSuccess) return e;
+    return cudaGetLastError();
+}
+
+template <class A>
+cudaError_t Launcher<A>::poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B,
+                                      cudaStream_t st) {
+    const unsigned nt = tiles_of(pl, nl, B);
+    if (pl.logN <= (u32)kMaxLogSlab) {
+        switch (pl.logN) {
+#define X(LS) case LS: return launch_row_polymul<A, LS, LS, true, true>(pl, limb0, a, b_ntt, c, B, nt, st);
+            GFHE_ROW_CASES(X)
+#undef X
+            default: return cudaErrorInvalidValue;
+        }
+    }
+    // high stages of a -> c (scratch), then the fused row pass against NTT(b), then the high inverse stages in place
+    if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, nullptr, nullptr, B, nt, st)) return e;
+    cudaError_t e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false, true>(pl, limb0, c, b_ntt, c, B, nt, st)
+                                             : launch_row_polymul<A, 12, 12, false, true>(pl, limb0, c, b_ntt, c, B, nt, st);
     if (e != cudaSuccess) return e;
     if ((e = launch_col_inv<A>(pl, limb0, c, c, B, nt, st)) != cudaSuccess) return e;
     return cudaGetLastError();

@@ -168,6 +168,11 @@ cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, con
     return pl.lazy ? Launcher<Lazy60>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st)
                    : Launcher<Harvey>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
 }
+cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
+    if (pl.w32) return Launcher<Shoup32>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
+    return pl.lazy ? Launcher<Lazy60>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st)
+                   : Launcher<Harvey>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
+}
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
     if (pl.logN <= 12) return 0;
     return ((size_t)nl * B * sizeof(u64)) << pl.logN;   // one operand-sized scratch

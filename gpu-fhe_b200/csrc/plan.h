@@ -60,6 +60,8 @@ struct Launcher {
     static cudaError_t ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
     static cudaError_t poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
                                 cudaStream_t st);
+    static cudaError_t poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B,
+                                    cudaStream_t st);
 };
 
 // plan.cu -- pick the policy of the plan; all operate on limbs [limb0, limb0 + nl), buffers are [nl, B, N]
@@ -68,6 +70,7 @@ cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
                             cudaStream_t st);
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B);
+cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st);
 
 // vec_kernels.cu
 cudaError_t launch_vec_op(int op, const Plan& pl, u32 limb0, u32 nl, const long long* a, const long long* b,

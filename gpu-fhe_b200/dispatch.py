@@ -171,6 +171,24 @@ def poly_mul(a, b, MOD):
     return A.wrap(out)
 
 
+def poly_mul_pre(a, b_ntt, MOD):
+    """iNTT(NTT(a) * b_ntt): a in the coefficient domain, b_ntt = NTT(b) cached by the caller."""
+    moduli = ring.resolve_moduli(MOD)
+    A = _Arg(a)
+    Bv = _Arg(b_ntt, A.t.device)
+    if A.shape != Bv.shape:
+        raise AssertionError("operands must have equal shapes")
+    L, B, N = _lbn(A.shape, len(moduli))
+    dev = A.t.device
+    plan = ring.get_plan(dev.index, N, moduli)
+    out = torch.empty_like(A.t)
+    if B == 0:
+        return A.wrap(out)
+    _capi.check(_capi.lib.gfhe_poly_mul_pre(plan.handle, 0, L, B, _ptr(A.t), _ptr(Bv.t), _ptr(out), _stream(dev)),
+                "gfhe_poly_mul_pre")
+    return A.wrap(out)
+
+
 # ---- NTT-domain-resident ops (SURVEY.md section 8f rows 2 and 4) ------------------------------------
 
 def mul_acc(a, b, MOD, stacked: bool):

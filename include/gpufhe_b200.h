@@ -11,6 +11,7 @@
  *   gfhe_ntt_inverse             <- /root/reference/arithmetic.py:18-19  (iNTT, an identity stub there)
  *   gfhe_plan_create             <- /root/reference/primitive.py:3-4     (placeholder for the roots of unity)
  *   gfhe_poly_mul                <- /root/reference/" polynomial.py":3-5 (module that would hold poly_mul)
+ *   gfhe_poly_mul_pre            <- the same product with one operand cached in the NTT domain
  *   gfhe_ntt_mul_acc             <- /root/reference/arithmetic.py:11-13 applied in the NTT domain (sum of pointwise
  *                                   products; the reference has no NTT-domain API -- SURVEY.md section 8f row 2)
  *   gfhe_automorphism            <- absent from the reference: a(X) -> a(X^k)
@@ -78,6 +79,12 @@ size_t gfhe_poly_mul_workspace_bytes(gfhe_plan_t plan, uint32_t num_limbs, uint3
 int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
                   const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_c,
                   void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Same product when b is ALREADY in the NTT domain (d_b_ntt = what gfhe_ntt_forward wrote for b, canonical residues):
+ * c = iNTT(NTT(a) .* d_b_ntt).  b's forward transform is skipped (a third of the work) -- for callers that multiply many
+ * polynomials by one cached operand.  No workspace.  c may alias neither input. */
+int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                      const uint64_t* d_a, const uint64_t* d_b_ntt, uint64_t* d_c, void* stream);
 
 /* out = (a op b) mod q_l, exact for ANY int64 inputs (Python % semantics, result in [0, q)).
  * Buffers are [num_limbs, inner]; limb l of the range uses modulus limb0 + l. */

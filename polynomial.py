@@ -7,6 +7,7 @@ cannot be imported by name; this one can).
     poly_sub(a, b, MOD)   same shape of call, difference
     poly_mul(a, b, MOD)   new: negacyclic product in Z_q[X]/(X^N+1) per RNS limb,
                           iNTT(NTT(a) * NTT(b)) as one fused GPU pipeline
+    poly_mul_pre(a, B)    a * b with B = NTT(b) cached by the caller (b's forward transform skipped)
     poly_mul_ntt(A, B)    NTT-domain pointwise product of operands that are already transformed
     poly_mac_ntt(As, Bs)  NTT-domain inner product sum_t As[t] * Bs[t] (key-switching style), one reduction per residue
     poly_mul_pair(a, b)   product of two 2-component pairs (a0 + a1 s)(b0 + b1 s) -> 3 components, 4 forward + 3 inverse
@@ -18,7 +19,7 @@ from arithmetic import _d
 
 __all__ = ["np", "vec_add", "vec_sub", "vec_mul", "NTT", "iNTT", "XXX",
            "find_psi", "ntt_primes", "is_probable_prime", "set_ring", "get_ring", "ring", "make_plan", "clear_plans",
-           "poly_add", "poly_sub", "poly_mul", "poly_mul_ntt", "poly_mac_ntt", "automorphism", "poly_mul_pair"]
+           "poly_add", "poly_sub", "poly_mul", "poly_mul_pre", "poly_mul_ntt", "poly_mac_ntt", "automorphism", "poly_mul_pair"]
 
 
 def poly_add(a, b, MOD):
@@ -34,6 +35,12 @@ def poly_mul(a, b, MOD=None):
     [L,1,1] array, or None to use the installed ring."""
     assert a.shape == b.shape
     return _d.poly_mul(a, b, MOD)
+
+
+def poly_mul_pre(a, b_ntt, MOD=None):
+    """poly_mul(a, b) given b_ntt = NTT(b): the fused pipeline without b's forward transform."""
+    assert a.shape == b_ntt.shape
+    return _d.poly_mul_pre(a, b_ntt, MOD)
 
 
 def poly_mul_ntt(a, b, MOD=None):

@@ -490,3 +490,23 @@ def test_w32_policy_all_sizes(cuda_device, logn, monkeypatch):
         assert torch.equal(P.NTT(ta), X) and torch.equal(P.poly_mul(ta, tb), c)
     monkeypatch.delenv("GFHE_NO_W32")
     P.clear_plans()
+
+
+@pytest.mark.parametrize("logn,bits", [(4, 60), (6, 30), (10, 50), (12, 60), (13, 61), (14, 30), (16, 60), (17, 60)])
+def test_poly_mul_pre_equals_poly_mul(cuda_device, logn, bits):
+    """One operand cached in the NTT domain: same words as the coefficient-domain product, every kernel shape/policy."""
+    import polynomial as P
+    N, L, B = 1 << logn, 2, 3
+    moduli = P.ntt_primes(bits, L)
+    a, b = rand_lbn(300 + logn, moduli, B, N), rand_lbn(400 + logn, moduli, B, N)
+    a[:, 0, :3] = np.array(moduli, dtype=np.uint64).reshape(2, 1) - 1
+    b[:, 0, :3] = np.array(moduli, dtype=np.uint64).reshape(2, 1) - 1
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    with P.ring(moduli):
+        Bn = P.NTT(tb)
+        c = P.poly_mul_pre(ta, Bn)
+        assert torch.equal(c, P.poly_mul(ta, tb))
+        assert torch.equal(Bn, P.NTT(tb)) and torch.equal(ta, dev_i64(a, cuda_device))   # inputs untouched
+    if logn <= 13:
+        R = oracle_ring(N, moduli)
+        assert np.array_equal(host_u64(c), R.poly_mul(a, b, fast=True))

@@ -29,8 +29,12 @@ struct __align__(16) LimbParams {
     u32 kshift;     // k - 17 (kred: y = x >> kshift fits 32 bits for x < 16q); valid when k >= 20
     u64 kmu;        // floor(2^(32 + kshift) / q) <= 2^16
     u64 r64;        // 2^64 mod q (folds the high word of a 128-bit accumulator, ring_kernels.cu)
+    // FP64 policy (q < 2^50): the same constants as doubles, each with its quotient companion c/q
+    double qd, qinv;           // q and 1/q
+    double ninv_d, ninv_q;     // N^-1 and N^-1/q
+    double w1ninv_d, w1ninv_q; // psi^-brv(1) * N^-1 and the same over q
 };
-static_assert(sizeof(LimbParams) == 96, "LimbParams layout");
+static_assert(sizeof(LimbParams) == 144, "LimbParams layout");
 
 // Layout of the warp-tiled twiddle copy (plan.cu fills it, ntt_core.cuh TwT0 reads it).
 constexpr u32 kT0Block = 15 * 32;   // entries per warp-tile
@@ -196,6 +200,11 @@ __device__ __forceinline__ u32 shoup32(u32 x, u32 w, u32 ws32, u32 nq) {
 //             (the API's layout), but every butterfly is 3 multiply + 4 add/min instructions instead of 9 + 11.
 struct Harvey {
     typedef u64 word;
+    static constexpr bool kFloat = false;
+    __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
+    __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
+    __device__ static __forceinline__ u64 from_raw(u64 v) { return v; }   // words of the intermediate buffers between passes
+    __device__ static __forceinline__ u64 to_raw(u64 v) { return v; }
     static constexpr bool kLazy = false;
     static constexpr int kFwdC = 2;   // forward offset/csub constant = kFwdC * q
     static constexpr int kInvC = 2;
@@ -204,6 +213,11 @@ struct Harvey {
 };
 struct Lazy60 {
     typedef u64 word;
+    static constexpr bool kFloat = false;
+    __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
+    __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
+    __device__ static __forceinline__ u64 from_raw(u64 v) { return v; }   // words of the intermediate buffers between passes
+    __device__ static __forceinline__ u64 to_raw(u64 v) { return v; }
     static constexpr bool kLazy = true;
     static constexpr int kFwdC = 4;   // T < 4q
     static constexpr int kInvC = 8;
@@ -212,11 +226,55 @@ struct Lazy60 {
 };
 struct Shoup32 {
     typedef u32 word;
+    static constexpr bool kFloat = false;
+    __device__ static __forceinline__ u32 from_u64(u64 v) { return (u32)v; }
+    __device__ static __forceinline__ u64 to_u64(u32 v) { return v; }
+    __device__ static __forceinline__ u32 from_raw(u64 v) { return (u32)v; }
+    __device__ static __forceinline__ u64 to_raw(u32 v) { return v; }
     static constexpr bool kLazy = false;
     static constexpr int kFwdC = 2;
     static constexpr int kInvC = 2;
     __device__ static __forceinline__ u32 mul(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
     __device__ static __forceinline__ u32 mul_exact(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
+};
+
+// ---- FP64 arithmetic for moduli below 2^50 -----------------------------------------------------------------------
+// B200 retires DFMA at the same rate as IMAD, on a pipe the integer kernels leave idle, and one DFMA pair gives the
+// exact 106-bit product of two 53-bit integers (h = fl(y*w), l = fma(y, w, -h)).  Residues are integer-valued doubles
+// kept in (-2^51, 2^51); twiddles are stored as {w, fl(w/q)} (bit patterns in the same ulonglong2 tables).
+//   fp_mulmod : y*w - rint(y*w/q)*q, exact, in [-0.75q, 0.75q] for |y| < 2^51   (6 FP64 instructions)
+//   fp_reduce : x - rint(x/q)*q, exact, in [-0.51q, 0.51q]                        (3 FP64 instructions)
+constexpr double kFpMagic = 6755399441055744.0;   // 1.5 * 2^52: fma(v, 1, M) - M = rint(v) for |v| < 2^51
+__device__ __forceinline__ double fp_mulmod(double y, double w, double wq, double q) {
+    const double c = fma(y, wq, kFpMagic) - kFpMagic;
+    const double h = y * w;
+    const double l = fma(y, w, -h);
+    return fma(-c, q, h) + l;
+}
+__device__ __forceinline__ double fp_reduce(double x, double q, double qinv) {
+    const double c = fma(x, qinv, kFpMagic) - kFpMagic;
+    return fma(-c, q, x);
+}
+__device__ __forceinline__ double fp_canon(double x, double q) { return x < 0.0 ? x + q : x; }   // [-q, q) -> [0, q)
+__device__ __forceinline__ double bits_to_double(u64 b) { return __longlong_as_double((long long)b); }
+
+struct Fp50 {
+    typedef double word;
+    static constexpr bool kFloat = true;
+    static constexpr bool kLazy = false;
+    static constexpr int kFwdC = 2;
+    static constexpr int kInvC = 2;
+    // v < 2^52: place v in the mantissa of 2^52 and subtract 2^52 (LOP3 + DADD, no conversion instruction)
+    __device__ static __forceinline__ double from_u64(u64 v) {
+        return __longlong_as_double((long long)(v | 0x4330000000000000ull)) - 4503599627370496.0;
+    }
+    // 0 <= v < 2^52, integer-valued
+    __device__ static __forceinline__ u64 to_u64(double v) {
+        return (u64)__double_as_longlong(v + 4503599627370496.0) & 0x000FFFFFFFFFFFFFull;
+    }
+    // between the two passes of a large transform the (signed, unreduced) doubles travel as their bit patterns
+    __device__ static __forceinline__ double from_raw(u64 v) { return __longlong_as_double((long long)v); }
+    __device__ static __forceinline__ u64 to_raw(double v) { return (u64)__double_as_longlong(v); }
 };
 
 }  // namespace gfhe

@@ -25,9 +25,9 @@
 #define GFHE_SYNC() __syncthreads()
 #endif
 #ifdef GFHE_EXP_NOGLD
-#define GFHE_GLD(T, expr, fake) ((T)(fake))
+#define GFHE_GLD(conv, expr, fake) conv((u64)(fake))
 #else
-#define GFHE_GLD(T, expr, fake) ((T)(expr))
+#define GFHE_GLD(conv, expr, fake) conv(expr)
 #endif
 
 namespace gfhe {
@@ -98,6 +98,28 @@ struct TwT0 {
 template <class A, int B_HI, int B_LO, class TW>
 __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq) {
     typedef typename A::word W;
+    if constexpr (A::kFloat) {
+        // FP64 policy: C = q, nq = 1/q.  Every value entering a stage is below 1.26q in magnitude: X is brought under
+        // 0.51q, the product is within 0.75q, so both outputs are again below 1.26q < 2^51.
+#pragma unroll
+        for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
+            const int b = B_HI - sidx;
+#pragma unroll
+            for (int hi = 0; hi < (8 >> b); ++hi) {
+                const ulonglong2 t = tw.get(b, hi);
+                const double w = bits_to_double(t.x), wq = bits_to_double(t.y);
+#pragma unroll
+                for (int lo = 0; lo < (1 << b); ++lo) {
+                    const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
+                    const double X = fp_reduce(r[ix], C, nq);
+                    const double T = fp_mulmod(r[iy], w, wq, C);
+                    r[ix] = X + T;
+                    r[iy] = X - T;
+                }
+            }
+        }
+        return;
+    } else {
 #pragma unroll
     for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
         const int b = B_HI - sidx;
@@ -115,19 +137,22 @@ __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const T
             }
         }
     }
+    }
 }
 
 // Reduction of a forward residue that feeds the pointwise product: [0, 2q) is enough for Lazy60.
 template <class A>
 __device__ __forceinline__ typename A::word fwd_semi(typename A::word x, typename A::word q, typename A::word nq, u32 kshift, u32 kmu) {
-    if constexpr (A::kLazy) return kred(x, kshift, kmu, nq);
+    if constexpr (A::kFloat) return fp_reduce(x, q, nq);                   // |x| <= 0.51q
+    else if constexpr (A::kLazy) return kred(x, kshift, kmu, nq);
     else return csub(csub(x, 2 * q), q);
 }
 
 // Full reduction of a forward residue to [0, q).
 template <class A>
 __device__ __forceinline__ typename A::word fwd_final(typename A::word x, typename A::word q, typename A::word nq, u32 kshift, u32 kmu) {
-    if constexpr (A::kLazy) return csub(kred(x, kshift, kmu, nq), q);   // [0,16q) -> [0,2q) -> [0,q)
+    if constexpr (A::kFloat) return fp_canon(fp_reduce(x, q, nq), q);     // -> [0, q)
+    else if constexpr (A::kLazy) return csub(kred(x, kshift, kmu, nq), q);   // [0,16q) -> [0,2q) -> [0,q)
     else return csub(csub(x, 2 * q), q);                                // [0,4q)
 }
 
@@ -144,6 +169,37 @@ template <class A, int B_HI, int B_LO, bool LAST, class TW>
 __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq,
                                           const LimbParams* __restrict__ Pg) {
     typedef typename A::word W;
+    if constexpr (A::kFloat) {
+        // FP64 policy: C = q, nq = 1/q.  Values entering a stage are below q in magnitude (canonical inputs, products
+        // within 0.75q, reduced sums within 0.51q), so U - V and U + V stay below 2q <= 2^51.
+#pragma unroll
+        for (int b = B_LO; b <= B_HI; ++b) {
+            if (LAST && b == B_HI) {
+                const double nd = __ldg(&Pg->ninv_d), nqd = __ldg(&Pg->ninv_q), wd = __ldg(&Pg->w1ninv_d), wqd = __ldg(&Pg->w1ninv_q);
+#pragma unroll
+                for (int lo = 0; lo < (1 << b); ++lo) {
+                    const int ix = lo, iy = ix + (1 << b);
+                    const double U = r[ix], V = r[iy];
+                    r[ix] = fp_canon(fp_mulmod(U + V, nd, nqd, C), C);
+                    r[iy] = fp_canon(fp_mulmod(U - V, wd, wqd, C), C);
+                }
+            } else {
+#pragma unroll
+                for (int hi = 0; hi < (8 >> b); ++hi) {
+                    const ulonglong2 t = tw.get(b, hi);
+                    const double w = bits_to_double(t.x), wq = bits_to_double(t.y);
+#pragma unroll
+                    for (int lo = 0; lo < (1 << b); ++lo) {
+                        const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
+                        const double U = r[ix], V = r[iy];
+                        r[ix] = fp_reduce(U + V, C, nq);
+                        r[iy] = fp_mulmod(U - V, w, wq, C);
+                    }
+                }
+            }
+        }
+        return;
+    } else {
 #pragma unroll
     for (int b = B_LO; b <= B_HI; ++b) {
         if (LAST && b == B_HI) {
@@ -178,15 +234,20 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
             }
         }
     }
+    }
 }
 
 // ---- shared-memory re-distribution ---------------------------------------------------------------
+template <class W> struct __align__(16) W2 { W x, y; };   // 16-byte pair of 8-byte words (u64 or double)
 template <int P0, class W>
 __device__ __forceinline__ void sm_store(W* sm, u32 tid, const W (&r)[kElems]) {
     W* p = sm + pad(elem_index<P0>(tid, 0));
     if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) *reinterpret_cast<ulonglong2*>(p + 2 * j) = make_ulonglong2(r[2 * j], r[2 * j + 1]);
+        for (int j = 0; j < 8; ++j) {
+            W2<W> v; v.x = r[2 * j]; v.y = r[2 * j + 1];
+            *reinterpret_cast<W2<W>*>(p + 2 * j) = v;
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[pad((u32)i << P0)] = r[i];
@@ -198,7 +259,7 @@ __device__ __forceinline__ void sm_load(const W* sm, u32 tid, W (&r)[kElems]) {
     if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(p + 2 * j);
+            const W2<W> v = *reinterpret_cast<const W2<W>*>(p + 2 * j);
             r[2 * j] = v.x; r[2 * j + 1] = v.y;
         }
     } else {

@@ -69,8 +69,13 @@ template <class W> struct LimbK { W q, nq, Cf, Ci; };
 template <class A>
 __device__ __forceinline__ LimbK<typename A::word> limb_consts(const LimbParams* __restrict__ Pg) {
     typedef typename A::word W;
+    if constexpr (A::kFloat) {   // FP64 policy: Cf = Ci = q, nq = 1/q (ntt_core.cuh)
+        const double q = __ldg(&Pg->qd), qi = __ldg(&Pg->qinv);
+        return LimbK<W>{q, qi, q, q};
+    } else {
     const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(&Pg->q2));   // {2q, -q mod 2^64}
     return LimbK<W>{(W)(v.x >> 1), (W)v.y, (W)((u64)(A::kFwdC / 2) * v.x), (W)((u64)(A::kInvC / 2) * v.x)};
+    }
 }
 template <class A>
 __device__ __forceinline__ void fwd_final_all(typename A::word (&r)[kElems], const LimbK<typename A::word>& K, const LimbParams* __restrict__ Pg) {
@@ -95,6 +100,30 @@ __device__ __forceinline__ void copy_out_padded(const u64* sm, u64* out, u32 tid
     for (int it = 0; it < 8; ++it) {
         const u32 e = 2u * (it * NT + tid);
         *reinterpret_cast<ulonglong2*>(out + e) = *reinterpret_cast<const ulonglong2*>(sm + pad(e));
+    }
+}
+// FP64 policy: canonical doubles in shared memory <-> canonical 64-bit integers in HBM
+template <int LOGT>
+__device__ __forceinline__ void copy_out_padded(const double* sm, u64* out, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const u32 e = 2u * (it * NT + tid);
+        const double2 v = *reinterpret_cast<const double2*>(sm + pad(e));
+        *reinterpret_cast<ulonglong2*>(out + e) = make_ulonglong2(Fp50::to_u64(v.x), Fp50::to_u64(v.y));
+    }
+}
+template <int LOGT>
+__device__ __forceinline__ void copy_in_padded(double* sm, const u64* in, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        ulonglong2 v[4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it) v[it] = *reinterpret_cast<const ulonglong2*>(in + 2u * ((4 * h + it) * NT + tid));
+#pragma unroll
+        for (int it = 0; it < 4; ++it)
+            *reinterpret_cast<double2*>(sm + pad(2u * ((4 * h + it) * NT + tid))) = make_double2(Fp50::from_u64(v[it].x), Fp50::from_u64(v[it].y));
     }
 }
 // 32-bit words in shared memory, 64-bit words in HBM: pad(e) is even for even e, so the pair is one 8-byte access
@@ -146,8 +175,13 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     const TwTab T = limb_tables(tabs, s.limb, logN);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
+    if (logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+    } else {
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+    }
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
     if constexpr (LOGT > 4) {
@@ -156,7 +190,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
         copy_out_padded<LOGT>(sm, out + s.g0, tid);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) out[s.g0 + i] = r[i];
+        for (int i = 0; i < kElems; ++i) out[s.g0 + i] = A::to_u64(r[i]);
     }
 }
 
@@ -179,12 +213,12 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
         sm_load<0>(sm, tid, r);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = (W)in[s.g0 + i];
+        for (int i = 0; i < kElems; ++i) r[i] = A::from_u64(in[s.g0 + i]);
     }
     slab_inv<A, LOGS, WHOLE>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = r[i];
+    for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);
 }
 
 // ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
@@ -233,13 +267,21 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     constexpr int P0 = Sched<LOGS>::p0(0);
     W r[kElems];
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+    for (int i = 0; i < kElems; ++i)
+        r[i] = WHOLE ? GFHE_GLD(A::from_u64, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i)
+                     : GFHE_GLD(A::from_raw, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
     slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
     fwd_semi_all<A>(r, K, Pg);
     if constexpr (BNTT) {
         tma_tile_wait(mbar);
         const u64* pb = smb + (tid << 4);   // this thread's 16 residues of NTT(b), same positions as r[]
-        if constexpr (sizeof(W) == 8) {
+        if constexpr (A::kFloat) {
+#pragma unroll
+            for (int i = 0; i < kElems; ++i) {
+                const double vb = fp_reduce(A::from_u64(pb[i]), K.q, K.nq);   // canonical [0,q) -> within 0.51q
+                r[i] = fp_mulmod(r[i], vb, vb * K.nq, K.q);
+            }
+        } else if constexpr (sizeof(W) == 8) {
             const u64 mu = __ldg(&Pg->bar_mu);
             const u32 bs = __ldg(&Pg->bar_shift);
 #pragma unroll
@@ -268,10 +310,14 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
         GFHE_SYNC();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
         tma_tile_wait(mbar);
     #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = (W)(smb + elem_index<P0>(tid, 0))[i << P0];
+        for (int i = 0; i < kElems; ++i) r[i] = WHOLE ? A::from_u64((smb + elem_index<P0>(tid, 0))[i << P0]) : A::from_raw((smb + elem_index<P0>(tid, 0))[i << P0]);
         slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
         fwd_semi_all<A>(r, K, Pg);
-        if constexpr (sizeof(W) == 8) {
+        if constexpr (A::kFloat) {   // |a|, |b| <= 0.51q: the same error-free product, quotient by 1/q
+            const W* pa = sm1 + pad(tid << 4);
+#pragma unroll
+            for (int i = 0; i < kElems; ++i) r[i] = fp_mulmod(pa[i], r[i], r[i] * K.nq, K.q);
+        } else if constexpr (sizeof(W) == 8) {
             const u64 mu = __ldg(&Pg->bar_mu);
             const u32 bs = __ldg(&Pg->bar_shift);
             const u64* pa = reinterpret_cast<const u64*>(sm1) + pad(tid << 4);
@@ -299,7 +345,7 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     }
     slab_inv<A, LOGS, WHOLE>(r, sm0, tid, Ti, s.off, K.Ci, K.nq, Pg);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = r[i];
+    for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -350,7 +396,7 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
     {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<8>(i)], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
     GFHE_SYNC();
@@ -362,11 +408,11 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
         fwd_round<A, 3, Geo::LO4>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         u64* p = out + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = r[i];
+        for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = A::to_raw(r[i]);
     } else {
         u64* p = out + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = r[i];
+        for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_raw(r[i]);
     }
 }
 
@@ -387,11 +433,11 @@ k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     if constexpr (Geo::TWO) {
         const u64* p = in + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<4>(i)], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<4>(i)], tid * 77u + i);
     } else {
         const u64* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(W, p[Geo::template roff<8>(i)], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);
     GFHE_SYNC();
@@ -404,7 +450,7 @@ k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
     inv_round<A, 3, Geo::LO8, true>(r, TwSm{tws, 1u}, K.Ci, K.nq, Pg);
     u64* p = out + Geo::template toff<8>(tid);
 #pragma unroll
-    for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = r[i];
+    for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_u64(r[i]);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -7,6 +7,7 @@
 //   inv[l][k] = { psi_l^-brv(k), floor(psi_l^-brv(k) * 2^64 / q_l) }
 // brv = bit reversal over log2(N) bits, so stage "m groups" reads entries [m, 2m) contiguously.
 #include <cstdlib>
+#include <cstring>
 #include <thread>
 #include <vector>
 #include "plan.h"
@@ -47,6 +48,8 @@ static void fill_limb_params(LimbParams& P, u64 q, u32 logN, u64 psi) {
         P.kshift = k - 17;
         P.kmu = (u64)((((u128)1) << (32 + P.kshift)) / q);
     }
+    P.qd = (double)q;
+    P.qinv = 1.0 / (double)q;
     if (logN) {
         const u64 N = 1ull << logN;
         P.ninv = h_powmod(N % q, q - 2, q);
@@ -55,18 +58,24 @@ static void fill_limb_params(LimbParams& P, u64 q, u32 logN, u64 psi) {
         const u64 w1 = h_powmod(psi_inv, N >> 1, q);   // psi^-brv(1) = psi^-(N/2)
         P.w1ninv = h_mulmod(w1, P.ninv, q);
         P.w1ninv_s = h_shoup(P.w1ninv, q);
+        P.ninv_d = (double)P.ninv;     P.ninv_q = (double)((long double)P.ninv / (long double)q);
+        P.w1ninv_d = (double)P.w1ninv; P.w1ninv_q = (double)((long double)P.w1ninv / (long double)q);
     }
 }
 
 // Sequential powers psi^0..psi^(N-1), scattered to bit-reversed positions.
-static void fill_tables(ulonglong2* fwd, ulonglong2* inv, u64 q, u32 logN, u64 psi) {
+static inline u64 d_bits(double d) { u64 b; std::memcpy(&b, &d, 8); return b; }
+// FP64 policy: {w, fl(w/q)} as bit patterns (x87 long double carries 64 bits, so the quotient is rounded once more to
+// double: relative error <= 2^-53 (1 + 2^-11), inside fp_mulmod's budget)
+static inline ulonglong2 fp_entry(u64 w, u64 q) { return make_ulonglong2(d_bits((double)w), d_bits((double)((long double)w / (long double)q))); }
+static void fill_tables(ulonglong2* fwd, ulonglong2* inv, u64 q, u32 logN, u64 psi, bool f64) {
     const u64 N = 1ull << logN;
     const u64 psi_inv = h_powmod(psi, 2 * N - 1, q);
     u64 pw = 1, pwi = 1;
     for (u64 e = 0; e < N; ++e) {
         const u32 k = h_brv((u32)e, logN);
-        fwd[k] = make_ulonglong2(pw, h_shoup(pw, q));
-        inv[k] = make_ulonglong2(pwi, h_shoup(pwi, q));
+        fwd[k] = f64 ? fp_entry(pw, q) : make_ulonglong2(pw, h_shoup(pw, q));
+        inv[k] = f64 ? fp_entry(pwi, q) : make_ulonglong2(pwi, h_shoup(pwi, q));
         pw = h_mulmod(pw, psi, q);
         pwi = h_mulmod(pwi, psi_inv, q);
     }
@@ -108,6 +117,10 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     pl->w32 = pl->max_bits <= 30;
     if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') { pl->lazy = false; pl->w32 = false; }
     if (const char* env = std::getenv("GFHE_NO_W32")) if (env[0] == '1') pl->w32 = false;
+    pl->f64 = !pl->w32 && pl->max_bits <= 50 && logN != 0;
+    if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->f64 = false;
+    if (const char* env = std::getenv("GFHE_NO_F64")) if (env[0] == '1') pl->f64 = false;
+    const bool f64 = pl->f64;
 
     std::vector<LimbParams> hp(L);
     for (u32 l = 0; l < L; ++l) fill_limb_params(hp[l], moduli[l], logN, logN ? psi[l] : 0);
@@ -129,7 +142,7 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
         for (unsigned t = 0; t < nthr; ++t)
             pool.emplace_back([=]() {
                 for (u32 l = t; l < L; l += nthr) {
-                    fill_tables(hf + l * N, hi + l * N, moduli[l], logN, psi[l]);
+                    fill_tables(hf + l * N, hi + l * N, moduli[l], logN, psi[l], f64);
                     fill_t0(hf0 + l * n0, hf + l * N, logN);
                     fill_t0(hi0 + l * n0, hi + l * N, logN);
                 }
@@ -154,22 +167,27 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
 extern template struct Launcher<Harvey>;
 extern template struct Launcher<Lazy60>;
 extern template struct Launcher<Shoup32>;
+extern template struct Launcher<Fp50>;
 
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::ntt_fwd(pl, limb0, nl, in, out, B, st);
+    if (pl.f64) return Launcher<Fp50>::ntt_fwd(pl, limb0, nl, in, out, B, st);
     return pl.lazy ? Launcher<Lazy60>::ntt_fwd(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_fwd(pl, limb0, nl, in, out, B, st);
 }
 cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::ntt_inv(pl, limb0, nl, in, out, B, st);
+    if (pl.f64) return Launcher<Fp50>::ntt_inv(pl, limb0, nl, in, out, B, st);
     return pl.lazy ? Launcher<Lazy60>::ntt_inv(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_inv(pl, limb0, nl, in, out, B, st);
 }
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
+    if (pl.f64) return Launcher<Fp50>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st)
                    : Launcher<Harvey>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
 }
 cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
+    if (pl.f64) return Launcher<Fp50>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st)
                    : Launcher<Harvey>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
 }

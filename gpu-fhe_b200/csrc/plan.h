@@ -26,6 +26,7 @@ struct Plan {
     u32 logN = 0;                      // 0: modulus set only (vec_* ops), no tables
     u32 L = 0;
     u32 max_bits = 0;                  // bit length of the largest modulus
+    bool f64 = false;                  // every modulus is below 2^50 (and not all below 2^30): the FP64 kernels and FP64-form tables
     bool w32 = false;                  // every modulus is below 2^30: the Shoup32 kernels are used
     bool lazy = false;                 // every modulus is in [2^19, 2^60): the Lazy60 kernels are used
     LimbParams* d_params = nullptr;    // [L]

@@ -510,3 +510,43 @@ def test_poly_mul_pre_equals_poly_mul(cuda_device, logn, bits):
     if logn <= 13:
         R = oracle_ring(N, moduli)
         assert np.array_equal(host_u64(c), R.poly_mul(a, b, fast=True))
+
+
+# ---------------------------------------------------------------------------------------------------
+# FP64 arithmetic policy (moduli below 2^50): exact by construction (error-free products), so it must give the same
+# words as the integer kernels and the C oracle for every size, modulus width and extreme input
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logn,bits", [(4, 50), (5, 50), (8, 31), (10, 50), (12, 50), (12, 40), (13, 50), (14, 45),
+                                       (16, 50), (17, 50), (18, 50)])
+def test_fp64_policy_all_sizes(cuda_device, logn, bits, monkeypatch):
+    import polynomial as P
+    N = 1 << logn
+    moduli = P.ntt_primes(bits, 2, N=max(N, 1 << 12))
+    assert all((1 << 30) <= q < (1 << 50) for q in moduli)
+    B = 3 if logn <= 16 else 1
+    a, b = rand_lbn(500 + logn, moduli, B, N), rand_lbn(600 + logn, moduli, B, N)
+    qm1 = np.array(moduli, dtype=np.uint64).reshape(2, 1) - 1
+    a[:, 0, :4] = qm1
+    b[:, 0, :4] = qm1
+    a[:, 0, 4] = 0
+    if B > 1:
+        a[:, 1, :] = qm1            # a whole polynomial of q-1 against random and against itself
+        b[:, 2, :] = a[:, 2, :]
+    R = oracle_ring(N, moduli)
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    monkeypatch.delenv("GFHE_NO_F64", raising=False)
+    P.clear_plans()
+    with P.ring(moduli):
+        X, c = P.NTT(ta), P.poly_mul(ta, tb)
+        back = P.iNTT(X)
+        pre = P.poly_mul_pre(ta, P.NTT(tb))
+    assert np.array_equal(host_u64(X), R.ntt(a, fast=True, nthreads=4))
+    assert torch.equal(back, ta)
+    assert np.array_equal(host_u64(c), R.poly_mul(a, b, fast=True, nthreads=4))
+    assert torch.equal(pre, c)
+    monkeypatch.setenv("GFHE_NO_F64", "1")
+    P.clear_plans()
+    with P.ring(moduli):
+        assert torch.equal(P.NTT(ta), X) and torch.equal(P.poly_mul(ta, tb), c) and torch.equal(P.iNTT(X), ta)
+    monkeypatch.delenv("GFHE_NO_F64")
+    P.clear_plans()

@@ -88,7 +88,8 @@ def main():
         ("polymul", 65536, 32, 16, 60), ("ntt", 65536, 32, 16, 60), ("intt", 65536, 32, 16, 60),   # config 4
     ]
     cases += [("polymul", 65536, 32, 16, 30), ("ntt", 65536, 32, 16, 30), ("intt", 65536, 32, 16, 30),   # 32-bit policy
-              ("polymul", 4096, 4, 256, 30), ("ntt", 16384, 8, 128, 30)]
+              ("polymul", 4096, 4, 256, 30), ("ntt", 16384, 8, 128, 30),
+              ("polymul", 65536, 32, 16, 50), ("ntt", 65536, 32, 16, 50), ("intt", 65536, 32, 16, 50), ("ntt", 16384, 8, 128, 50)]   # FP64 policy
     grid = [1, 4, 16, 64] if not args.quick else [1, 16]
     for L in grid:                                                              # config 5: N = 2^17 sweep
         for B in grid:

@@ -99,11 +99,14 @@ template <class A, int B_HI, int B_LO, class TW>
 __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq) {
     typedef typename A::word W;
     if constexpr (A::kFloat) {
-        // FP64 policy: C = q, nq = 1/q.  Every value entering a stage is below 1.26q in magnitude: X is brought under
-        // 0.51q, the product is within 0.75q, so both outputs are again below 1.26q < 2^51.
+        // FP64 policy: C = q, nq = 1/q.  A product is within (0.5 + |y|/8q) q of zero (|y| < 2^51, q < 2^50).  X is brought
+        // under q/2 at the first and third stage of a round only: with inputs below 1.9q the outputs of a reducing stage are
+        // below 0.5 + 0.74 = 1.24q, those of the following stage below 1.24 + 0.5 + 1.24/8 = 1.9q < 2^51, so every round
+        // maps (-1.9q, 1.9q) to itself.
 #pragma unroll
         for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
             const int b = B_HI - sidx;
+            const bool reduce_x = (sidx & 1) == 0;
 #pragma unroll
             for (int hi = 0; hi < (8 >> b); ++hi) {
                 const ulonglong2 t = tw.get(b, hi);
@@ -111,7 +114,7 @@ __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const T
 #pragma unroll
                 for (int lo = 0; lo < (1 << b); ++lo) {
                     const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
-                    const double X = fp_reduce(r[ix], C, nq);
+                    const double X = reduce_x ? fp_reduce(r[ix], C, nq) : r[ix];
                     const double T = fp_mulmod(r[iy], w, wq, C);
                     r[ix] = X + T;
                     r[iy] = X - T;

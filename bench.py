@@ -204,6 +204,8 @@ def run_b200(args, rank, world, local_rank):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # several ranks on one box: keep each rank's pinned buffers and copy threads on its GPU's NUMA node (e2e leg)
+    prev_affinity = shard.bind_to_gpu_numa(local_rank) if world > 1 and not os.environ.get("GFHE_BENCH_NO_NUMA") else None
     B = B_PER_GPU * world
     sh = shard.partition(L_TOTAL, B, world, rank)
     assert sh.g_b == 1 and sh.num_limbs * sh.num_batch == UNITS_PER_GPU
@@ -344,6 +346,8 @@ def run_b200(args, rank, world, local_rank):
         del full
 
     clocks.stop = True
+    if prev_affinity:
+        os.sched_setaffinity(0, prev_affinity)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

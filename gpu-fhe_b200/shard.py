@@ -62,3 +62,26 @@ def all_gather_limbs(local: torch.Tensor, sh: Shard, group=None) -> torch.Tensor
     if sh.g_b == 1:
         return flat.reshape(sh.g_l * l, b, n)       # limb-outermost layout: no repacking needed
     return flat.reshape(sh.g_l, sh.g_b, l, b, n).permute(0, 2, 1, 3, 4).reshape(sh.g_l * l, sh.g_b * b, n)
+
+
+def bind_to_gpu_numa(device_index: int):
+    """Pin the calling process to the CPU cores NVML reports as local to `device_index`, so that the pinned host buffers
+    it allocates next (first-touch) and the threads that drive the copies sit on the GPU's own NUMA node.  Matters for
+    the host-buffer entry points when several ranks share one box: without it the ranks' PCIe traffic crosses the
+    socket interconnect.  Returns the previous affinity set (pass it to os.sched_setaffinity to undo), or None."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {i for i in range(ncpu) if (int(words[i // 64]) >> (i % 64)) & 1}
+        prev = os.sched_getaffinity(0)
+        cpus &= prev
+        if cpus and cpus != prev:
+            os.sched_setaffinity(0, cpus)
+            return prev
+    except Exception:
+        return None
+    return None

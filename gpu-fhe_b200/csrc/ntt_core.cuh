@@ -164,6 +164,16 @@ __device__ __forceinline__ typename A::word fwd_final(typename A::word x, typena
 // of its inputs are of the same kind.  A pair of products needs no conditional subtraction (12 of the 32 in a round).
 __host__ __device__ constexpr bool inv_pair_is_fresh(int b, int b_lo, int lo) { return b > b_lo && ((lo >> (b - 1)) & 1) != 0; }
 
+// The same idea for the FP64 policy.  Kind of register i BEFORE stage k of a round (stage k works on local bit b_lo + k):
+//   0 = S, anything up to q - 1 in magnitude (round entry; an unreduced sum of two R),
+//   1 = R, a reduced sum (<= (q-1)/2),   2 = P, a fresh product (<= 0.75q).
+// Both inputs of a pair have the same kind.  R + R stays unreduced (it is an S); S + S and P + P are reduced (|sum| < 2q).
+__host__ __device__ constexpr int fp_inv_kind(int k, int b_lo, int i) {
+    int kind = 0;
+    for (int j = 1; j <= k; ++j) kind = ((i >> (b_lo + j - 1)) & 1) ? 2 : (kind == 1 ? 0 : 1);
+    return kind;
+}
+
 // ---- one round of inverse (GS) stages on local bits B_LO..B_HI --------------------------------
 // C = A::kInvC * q: residues stay in [0, C) (Harvey 2q, Lazy60 8q).
 // LAST: local bit B_HI is the final stage of the whole transform; it multiplies by N^-1
@@ -173,8 +183,8 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
                                           const LimbParams* __restrict__ Pg) {
     typedef typename A::word W;
     if constexpr (A::kFloat) {
-        // FP64 policy: C = q, nq = 1/q.  Values entering a stage are below q in magnitude (canonical inputs, products
-        // within 0.75q, reduced sums within 0.51q), so U - V and U + V stay below 2q <= 2^51.
+        // FP64 policy: C = q, nq = 1/q.  Values entering a round are at most q - 1 in magnitude, so U - V and U + V stay
+        // below 2q - 2 < 2^51; fp_inv_kind tracks which sums may stay unreduced (9 of the 32 in a round).
 #pragma unroll
         for (int b = B_LO; b <= B_HI; ++b) {
             if (LAST && b == B_HI) {
@@ -195,7 +205,7 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
                     for (int lo = 0; lo < (1 << b); ++lo) {
                         const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
                         const double U = r[ix], V = r[iy];
-                        r[ix] = fp_reduce(U + V, C, nq);
+                        r[ix] = fp_inv_kind(b - B_LO, B_LO, ix) == 1 ? U + V : fp_reduce(U + V, C, nq);
                         r[iy] = fp_mulmod(U - V, w, wq, C);
                     }
                 }

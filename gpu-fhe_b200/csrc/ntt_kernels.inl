@@ -175,7 +175,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     const TwTab T = limb_tables(tabs, s.limb, logN);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
-    if (logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words
+    if (A::kFloat && logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words (they differ from canonical ones for the FP64 policy only)
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
     } else {
@@ -184,11 +184,19 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     }
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
+#ifdef GFHE_EXP_DIRECTST   // experiment: 16-byte stores straight from the registers (each lane writes its own 128-byte row)
+    if constexpr (LOGT > 4) {
+        u64* po = out + s.g0 + (tid << 4);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<ulonglong2*>(po + 2 * j) = make_ulonglong2(A::to_u64(r[2 * j]), A::to_u64(r[2 * j + 1]));
+    } else {
+#else
     if constexpr (LOGT > 4) {
         sm_store<0>(sm, tid, r);   // own 128-byte row: no hazard with the preceding sm_load<0>
         GFHE_SYNC();
         copy_out_padded<LOGT>(sm, out + s.g0, tid);
     } else {
+#endif
 #pragma unroll
         for (int i = 0; i < kElems; ++i) out[s.g0 + i] = A::to_u64(r[i]);
     }

@@ -373,6 +373,22 @@ def run_b200(args, rank, world, local_rank):
                "note": "oracle/ntt_oracle.c (Shoup/Harvey flavour, pthreads over limb-polynomials); the reference "
                        "repo itself has no NTT/poly-mul to time"}
 
+    # the element-wise family the reference DOES implement (arithmetic.py:3-13): its statement `(a + b) % MOD` /
+    # `(a * b) % MOD` on dtype=object numpy arrays (the only mode that is exact for 60-bit moduli), one host core, on a
+    # 2^20-residue sample of the same operands; next to it the GPU kernels' rate for the same ops
+    cpu_vec = None
+    if cpu is not None:
+        n_s = 1 << 20
+        xa = a_h.reshape(-1)[:n_s].astype(object)
+        xb = b_h.reshape(-1)[:n_s].astype(object)
+        q0 = int(moduli[0])
+        t0 = time.perf_counter(); _ = (xa + xb) % q0; t_add = time.perf_counter() - t0
+        t0 = time.perf_counter(); _ = (xa * xb) % q0; t_mul = time.perf_counter() - t0
+        cpu_vec = {"unit": "residue/s", "cores": 1, "kind": "port",
+                   "sample": "2^20 residues of operand a, b (limb 0), numpy dtype=object, statement of arithmetic.py:5,13",
+                   "vec_add": n_s / t_add, "vec_mul": n_s / t_mul,
+                   "gpu_vec_add": UNITS_PER_GPU * N / (ms_vadd * 1e-3), "gpu_pointwise_mul": UNITS_PER_GPU * N / (ms_mac1 * 1e-3)}
+
     line = {
         "metric": "limb_poly_mul_per_s", "value": value, "unit": "limb-poly-mul/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_total / K,
@@ -398,6 +414,7 @@ def run_b200(args, rank, world, local_rank):
                 "ms_per_step": e2e_s / e2e_steps * 1e3,
                 "h2d_bytes_per_step": int(2 * a_h.nbytes), "d2h_bytes_per_step": int(a_h.nbytes),
                 "api": "gfhe_poly_mul_host (pinned host arrays; limb groups pipelined H2D/kernels/D2H)"},
+        "cpu_baseline_vec_ops": cpu_vec,
         "gather": {"all_gather_ms": gather_ms, "bytes_out_per_rank": int(a_h.nbytes) * world} if world > 1 else None,
         "gpu_launches": int(round(sum(k["launches_per_step"] for k in kernels.values()) * K)) if kernels else 3 * K,
         "clocks": clocks.summary(),

@@ -550,3 +550,39 @@ def test_fp64_policy_all_sizes(cuda_device, logn, bits, monkeypatch):
         assert torch.equal(P.NTT(ta), X) and torch.equal(P.poly_mul(ta, tb), c) and torch.equal(P.iNTT(X), ta)
     monkeypatch.delenv("GFHE_NO_F64")
     P.clear_plans()
+
+
+def test_empty_and_non_contiguous_operands(cuda_device):
+    """Edge cases of the marshalling layer: zero-sized batches come back empty, strided views are made contiguous,
+    inputs are never written."""
+    import polynomial as P
+    N, L = 256, 2
+    moduli = P.ntt_primes(60, L)
+    empty = torch.empty((L, 0, N), dtype=torch.int64, device=cuda_device)
+    with P.ring(moduli):
+        assert tuple(P.NTT(empty).shape) == (L, 0, N)
+        assert tuple(P.iNTT(empty).shape) == (L, 0, N)
+        assert tuple(P.poly_mul(empty, empty).shape) == (L, 0, N)
+        assert tuple(P.poly_mul_pre(empty, empty).shape) == (L, 0, N)
+        assert tuple(P.poly_mul_ntt(empty, empty).shape) == (L, 0, N)
+        assert tuple(P.automorphism(empty, 3).shape) == (L, 0, N)
+    big = dev_i64(rand_lbn(77, moduli, 4, 2 * N), cuda_device)
+    view = big[:, ::2, :N]                     # non-contiguous in two dimensions
+    assert not view.is_contiguous()
+    keep = big.clone()
+    with P.ring(moduli):
+        X = P.NTT(view)
+        assert torch.equal(X, P.NTT(view.contiguous()))
+        assert torch.equal(P.iNTT(X), view)
+        c = P.poly_mul(view, view)
+        assert torch.equal(c, P.poly_mul(view.contiguous(), view.contiguous()))
+    assert torch.equal(big, keep)
+    # [B, N] and [N] operands with a single modulus
+    q = moduli[0]
+    x = dev_i64(rand_lbn(78, [q], 1, N)[0, 0], cuda_device)
+    assert tuple(P.NTT(x, MOD=q).shape) == (N,)
+    assert torch.equal(P.iNTT(P.NTT(x, MOD=q), MOD=q), x)
+    with pytest.raises(ValueError):
+        P.NTT(big, MOD=[q, q, q])              # three moduli, leading dimension 2
+    with pytest.raises(RuntimeError):
+        P.set_ring(None); P.NTT(x)             # no ring installed and no MOD=

@@ -279,6 +279,12 @@ def run_b200(args, rank, world, local_rank):
     kernels = {names[i].decode(): {"ms_per_launch": tot[i] / cnt[i], "launches_per_step": cnt[i] / (K + 1)} for i in range(max(nk, 0))}
     # ---- forward NTT throughput (second half of the metric)
     ms_ntt = timed(step_ntt, K, W)
+
+    def step_intt():
+        rc = lib.gfhe_ntt_inverse(plan.handle, 0, nl, nb, da.data_ptr(), dc.data_ptr(), st)
+        if rc:
+            raise RuntimeError(_capi.error_string(rc))
+    ms_intt = timed(step_intt, K, W)
     # ---- NTT-domain-resident kernels: pure HBM streaming, timed the same way
     inner = nb * N
     da4 = da.unsqueeze(0).expand(4, nl, nb, N).contiguous()
@@ -409,7 +415,9 @@ def run_b200(args, rank, world, local_rank):
                                   ("automorphism_ntt", ms_auto, 16), ("vec_add", ms_vadd, 24),
                                   ("poly_mul_pre (one operand cached in NTT form)", ms_pre, 24))},
         "ntt": {"metric": "limb_ntt_per_s", "value": ntt_value, "unit": "limb-NTT/s", "ms_per_step": ms_ntt / K,
-                "achieved_GBs": ntt_gbs, "frac": ntt_gbs / peak, "frac_of_8TBs_nominal": ntt_gbs / 8000.0},
+                "achieved_GBs": ntt_gbs, "frac": ntt_gbs / peak, "frac_of_8TBs_nominal": ntt_gbs / 8000.0,
+                "inverse": {"value": units * K / (ms_intt * 1e-3), "ms_per_step": ms_intt / K,
+                            "frac": ALG_BYTES_NTT * UNITS_PER_GPU / (ms_intt / K * 1e-3) / 1e9 / peak}},
         "e2e": {"value": units * e2e_steps / e2e_s, "unit": "limb-poly-mul/s", "steps": e2e_steps,
                 "ms_per_step": e2e_s / e2e_steps * 1e3,
                 "h2d_bytes_per_step": int(2 * a_h.nbytes), "d2h_bytes_per_step": int(a_h.nbytes),

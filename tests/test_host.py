@@ -115,3 +115,16 @@ def test_partition():
     assert len(cover) == 16
     with pytest.raises(ValueError):
         shard.partition(1, 3, 2, 0)
+
+
+def test_numa_binding_helper_is_harmless_without_nvml(built_lib):
+    """shard.bind_to_gpu_numa returns None (and changes nothing) when NVML has no device to ask."""
+    import os
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import shard
+    before = os.sched_getaffinity(0)
+    prev = shard.bind_to_gpu_numa(0)
+    if prev is None:
+        assert os.sched_getaffinity(0) == before
+    else:
+        os.sched_setaffinity(0, prev)

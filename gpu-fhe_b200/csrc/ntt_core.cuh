@@ -95,7 +95,17 @@ struct TwT0 {
 // C = A::kFwdC * q.  Harvey: residues in [0,4q), X is brought under 2q every stage.  Lazy60: residues
 // in [0,16q); the product is < 4q, so X grows by 4q per stage and is brought under 8q at the first
 // and third stage of a round (every round therefore maps [0,16q) to [0,16q)).
-template <class A, int B_HI, int B_LO, class TW>
+// Lazy60 range schedule: the bound (in units of q) of every residue before stage `nst` of a chain of forward stages that
+// starts from `entry`.  X is brought under 8q when the bound exceeds 12 (X + T must stay below 16q), then both outputs
+// gain 4q.  From entry 16 this is "subtract at every second stage"; from canonical inputs (entry 1) the first three
+// stages need nothing.
+__host__ __device__ constexpr int fwd_bound(int entry, int nst) {
+    int b = entry;
+    for (int s = 0; s < nst; ++s) { if (b > 12) b = 8; b += 4; }
+    return b;
+}
+
+template <class A, int B_HI, int B_LO, class TW, int ENTRY = 16>
 __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq) {
     typedef typename A::word W;
     if constexpr (A::kFloat) {
@@ -126,7 +136,7 @@ __device__ __forceinline__ void fwd_round(typename A::word (&r)[kElems], const T
 #pragma unroll
     for (int sidx = 0; sidx <= B_HI - B_LO; ++sidx) {
         const int b = B_HI - sidx;
-        const bool reduce_x = !A::kLazy || (sidx & 1) == 0;
+        const bool reduce_x = !A::kLazy || fwd_bound(ENTRY, sidx) > 12;
 #pragma unroll
         for (int hi = 0; hi < (8 >> b); ++hi) {
             const ulonglong2 t = tw.get(b, hi);
@@ -309,20 +319,21 @@ __device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
 // On entry r[] holds the layout of round 0 (window at bit p0(0)); on exit the layout of the last round
 // (window at bit 0: 16 contiguous residues per thread).  The slab may be a tile of several independent
 // 2^LOGS-point sub-transforms (tid then spans more than 2^(LOGS-4) threads): nothing here depends on it.
-template <class A, int LOGS>
+template <class A, int LOGS, int ENTRY = 16>
 __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
                                          typename A::word C, typename A::word nq) {
     using S = Sched<LOGS>;
+    // stages done before round k: LOGS - top(k); ENTRY is the range bound of the slab's inputs (fwd_bound)
     {
         constexpr int P0 = S::p0(0);
-        fwd_round<A, S::top(0) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
+        fwd_round<A, S::top(0) - 1 - P0, 0, decltype(round_tw<P0>(T, off, tid)), ENTRY>(r, round_tw<P0>(T, off, tid), C, nq);
     }
     if constexpr (S::NR > 1) {
         constexpr int PP = S::p0(0), P0 = S::p0(1);
         sm_store<PP>(sm, tid, r);
         GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
-        fwd_round<A, S::top(1) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
+        fwd_round<A, S::top(1) - 1 - P0, 0, decltype(round_tw<P0>(T, off, tid)), fwd_bound(ENTRY, LOGS - S::top(1))>(r, round_tw<P0>(T, off, tid), C, nq);
     }
     if constexpr (S::NR > 2) {
         constexpr int PP = S::p0(1), P0 = S::p0(2);
@@ -330,7 +341,7 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
         sm_store<PP>(sm, tid, r);
         GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
-        fwd_round<A, S::top(2) - 1 - P0, 0>(r, round_tw<P0>(T, off, tid), C, nq);
+        fwd_round<A, S::top(2) - 1 - P0, 0, decltype(round_tw<P0>(T, off, tid)), fwd_bound(ENTRY, LOGS - S::top(2))>(r, round_tw<P0>(T, off, tid), C, nq);
     }
 }
 

@@ -278,7 +278,7 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     for (int i = 0; i < kElems; ++i)
         r[i] = WHOLE ? GFHE_GLD(A::from_u64, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i)
                      : GFHE_GLD(A::from_raw, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
-    slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
+    slab_fwd<A, LOGS, WHOLE ? 1 : 16>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);   // whole polynomial: canonical inputs
     fwd_semi_all<A>(r, K, Pg);
     if constexpr (BNTT) {
         tma_tile_wait(mbar);
@@ -319,7 +319,7 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
         tma_tile_wait(mbar);
     #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = WHOLE ? A::from_u64((smb + elem_index<P0>(tid, 0))[i << P0]) : A::from_raw((smb + elem_index<P0>(tid, 0))[i << P0]);
-        slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);
+        slab_fwd<A, LOGS, WHOLE ? 1 : 16>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);   // whole polynomial: canonical inputs
         fwd_semi_all<A>(r, K, Pg);
         if constexpr (A::kFloat) {   // |a|, |b| <= 0.51q: the same error-free product, quotient by 1/q
             const W* pa = sm1 + pad(tid << 4);
@@ -408,12 +408,12 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
     }
     tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
     GFHE_SYNC();
-    fwd_round<A, 3, Geo::LO8>(r, TwSm{tws, 1u}, K.Cf, K.nq);
+    fwd_round<A, 3, Geo::LO8, TwSm, 1>(r, TwSm{tws, 1u}, K.Cf, K.nq);   // canonical inputs: the range schedule starts from q
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
         GFHE_SYNC();
         sm_load<4>(sm, tid, r);
-        fwd_round<A, 3, Geo::LO4>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
+        fwd_round<A, 3, Geo::LO4, TwSm, fwd_bound(1, 4 - Geo::LO8)>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         u64* p = out + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = A::to_raw(r[i]);

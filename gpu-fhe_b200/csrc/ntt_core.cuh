@@ -188,7 +188,9 @@ __host__ __device__ constexpr int fp_inv_kind(int k, int b_lo, int i) {
 // C = A::kInvC * q: residues stay in [0, C) (Harvey 2q, Lazy60 8q).
 // LAST: local bit B_HI is the final stage of the whole transform; it multiplies by N^-1
 // (folded: U' = (U+V)*N^-1, V' = (U-V)*psi^-brv(1)*N^-1) with the exact product and fully reduces to [0, q).
-template <class A, int B_HI, int B_LO, bool LAST, class TW>
+// FRESH: the round's inputs are canonical residues (first round of a stand-alone inverse transform), so the first stage
+// needs no conditional subtraction either.
+template <class A, int B_HI, int B_LO, bool LAST, class TW, bool FRESH = false>
 __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const TW tw, typename A::word C, typename A::word nq,
                                           const LimbParams* __restrict__ Pg) {
     typedef typename A::word W;
@@ -245,7 +247,7 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
                 for (int lo = 0; lo < (1 << b); ++lo) {
                     const int ix = (hi << (b + 1)) + lo, iy = ix + (1 << b);
                     const W U = r[ix], V = r[iy];
-                    if (A::kLazy && inv_pair_is_fresh(b, B_LO, lo)) {
+                    if (A::kLazy && (inv_pair_is_fresh(b, B_LO, lo) || (FRESH && b == B_LO))) {
                         // both inputs are products of the previous stage, < 4q: the sum is < 8q as it stands
                         r[ix] = U + V;
                         r[iy] = A::mul(U - V + (C >> 1), t.x, t.y, nq);
@@ -348,27 +350,27 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
 // ---- inverse transform of a slab: the LOGS low stages, bottom bit first --------------------------
 // Entry layout: window at bit 0; exit layout: window at bit p0(0).
 // LAST: the slab is the whole polynomial (N == 2^LOGS), so the top stage folds N^-1.
-template <class A, int LOGS, bool LAST>
+template <class A, int LOGS, bool LAST, bool FRESH = false>
 __device__ __forceinline__ void slab_inv(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
                                          typename A::word C, typename A::word nq, const LimbParams* __restrict__ Pg) {
     using S = Sched<LOGS>;
     if constexpr (S::NR > 2) {
         constexpr int P0 = S::p0(2), PN = S::p0(1);
-        inv_round<A, S::top(2) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
+        inv_round<A, S::top(2) - 1 - P0, 0, false, decltype(round_tw<P0>(T, off, tid)), FRESH>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
         GFHE_SYNC();
         sm_load<PN>(sm, tid, r);
     }
     if constexpr (S::NR > 1) {
         constexpr int P0 = S::p0(1), PN = S::p0(0);
-        inv_round<A, S::top(1) - 1 - P0, 0, false>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
+        inv_round<A, S::top(1) - 1 - P0, 0, false, decltype(round_tw<P0>(T, off, tid)), FRESH && S::NR == 2>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
         sm_store<P0>(sm, tid, r);
         GFHE_SYNC();
         sm_load<PN>(sm, tid, r);
     }
     {
         constexpr int P0 = S::p0(0);
-        inv_round<A, S::top(0) - 1 - P0, 0, LAST>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
+        inv_round<A, S::top(0) - 1 - P0, 0, LAST, decltype(round_tw<P0>(T, off, tid)), FRESH && S::NR == 1>(r, round_tw<P0>(T, off, tid), C, nq, Pg);
     }
 }
 

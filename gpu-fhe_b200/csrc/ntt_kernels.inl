@@ -223,7 +223,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = A::from_u64(in[s.g0 + i]);
     }
-    slab_inv<A, LOGS, WHOLE>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);
+    slab_inv<A, LOGS, WHOLE, true>(r, sm, tid, T, s.off, K.Ci, K.nq, Pg);   // inputs of an inverse transform are canonical
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);

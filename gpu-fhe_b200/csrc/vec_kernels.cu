@@ -29,12 +29,20 @@ k_vec(const long long* __restrict__ a, const long long* __restrict__ b, long lon
         const longlong2* b2 = reinterpret_cast<const longlong2*>(b + row);
         longlong2* o2 = reinterpret_cast<longlong2*>(out + row);
         const u64 n2 = inner >> 1;
-        for (; i < n2; i += stride) {
-            const longlong2 x = a2[i], y = b2[i];
+        for (; i + stride < n2; i += 2 * stride) {   // two 16-byte load pairs in flight per thread, streaming cache hints
+            const longlong2 x0 = __ldcs(a2 + i), y0 = __ldcs(b2 + i), x1 = __ldcs(a2 + i + stride), y1 = __ldcs(b2 + i + stride);
+            longlong2 z0, z1;
+            z0.x = vec_elem<OP>(x0.x, y0.x, P); z0.y = vec_elem<OP>(x0.y, y0.y, P);
+            z1.x = vec_elem<OP>(x1.x, y1.x, P); z1.y = vec_elem<OP>(x1.y, y1.y, P);
+            __stcs(o2 + i, z0);
+            __stcs(o2 + i + stride, z1);
+        }
+        if (i < n2) {
+            const longlong2 x = __ldcs(a2 + i), y = __ldcs(b2 + i);
             longlong2 z;
             z.x = vec_elem<OP>(x.x, y.x, P);
             z.y = vec_elem<OP>(x.y, y.y, P);
-            o2[i] = z;
+            __stcs(o2 + i, z);
         }
     } else {
         for (; i < inner; i += stride) out[row + i] = vec_elem<OP>(a[row + i], b[row + i], P);

@@ -18,6 +18,7 @@
 // /root/reference/" polynomial.py":3-5.
 // This file is a template body: ntt_harvey.cu and ntt_lazy.cu include it and instantiate Launcher<A>
 // for one arithmetic policy each (modarith.cuh), so the two sets of kernels compile in parallel.
+#include <cstdlib>
 #include "ntt_core.cuh"
 #include "plan.h"
 
@@ -356,6 +357,125 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);
 }
 
+// ---- persistent form of the fused row pass (two-pass transforms only) ---------------------------------------------------
+// One CTA per resident slot loops over tiles; the NEXT tile's operands are fetched by TMA bulk copies while the current
+// tile is computed, so no CTA ever waits for HBM at its start:
+//   a' -> the stash buffer (free once the pointwise product has read NTT(a)), landing during the inverse transform
+//   b' -> b's landing buffer (free once b has been read), landing during fwd(b), the product and the inverse transform
+// mbarrier phase `it & 1` of barA / barB belongs to loop trip `it`.
+__device__ __forceinline__ void mbar_init(u64* mbar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
+}
+__device__ __forceinline__ void tma_tile_issue(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
+    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* mbar, u32 parity) {
+    const u32 bar = smem_u32(mbar);
+    u32 done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+
+template <class A, int LOGS, int LOGT>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+k_row_polymul_persist(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0, u32 ntiles) {
+    typedef typename A::word W;
+    extern __shared__ __align__(16) u64 smem[];
+    W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
+    u64* sa = smem + padded_words(LOGT);                           // a's landing buffer (linear u64), then the stash of NTT(a)
+    W* sm1 = reinterpret_cast<W*>(sa);
+    u64* smb = smem + 2 * padded_words(LOGT);                      // b's landing buffer
+    u64* barA = smb + (1 << LOGT);
+    u64* barB = barA + 1;
+    const u32 tid = threadIdx.x;
+    constexpr u32 kTileBytes = (u32)sizeof(u64) << LOGT;
+    constexpr int P0 = Sched<LOGS>::p0(0);
+    if (tid == 0) {
+        mbar_init(barA); mbar_init(barB);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const u64 g0 = (u64)blockIdx.x << LOGT;
+        tma_tile_issue(sa, a + g0, kTileBytes, barA);
+        tma_tile_issue(smb, b + g0, kTileBytes, barB);
+    }
+    __syncthreads();
+    u32 it = 0;
+#pragma unroll 1
+    for (u32 tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const u32 par = it & 1u;
+        const u32 next = tile + gridDim.x;
+        TileId s;
+        s.g0 = (u64)tile << LOGT;
+        s.off = (u32)s.g0 & ((1u << logN) - 1u);
+        s.limb = limb0 + (u32)(s.g0 >> logN) / B;
+        const LimbParams* __restrict__ Pg = tf.params + s.limb;
+        const LimbK<W> K = limb_consts<A>(Pg);
+        const TwTab Tf = limb_tables(tf, s.limb, logN);
+        W r[kElems];
+        mbar_wait(barA, par);
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) r[i] = A::from_raw((sa + elem_index<P0>(tid, 0))[i << P0]);
+        slab_fwd<A, LOGS>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);   // its exchange barrier also orders every read of sa before the stash
+        fwd_semi_all<A>(r, K, Pg);
+        sm_store<0>(sm1, tid, r);
+        __syncthreads();
+        mbar_wait(barB, par);
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) r[i] = A::from_raw((smb + elem_index<P0>(tid, 0))[i << P0]);
+        // per-phase constants are re-derived from an opaque copy of the limb index: kept live from the top of the trip (or,
+        // for twiddles, from a's transform into b's) they spill ~40 registers under the 128-register cap
+        u32 limb_b = s.limb;
+        asm volatile("" : "+r"(limb_b));
+        slab_fwd<A, LOGS>(r, sm0, tid, limb_tables(tf, limb_b, logN), s.off, K.Cf, K.nq);   // ... and every read of smb before the refill below
+        if (tid == 0 && next < ntiles) tma_tile_issue(smb, b + ((u64)next << LOGT), kTileBytes, barB);
+        fwd_semi_all<A>(r, K, Pg);
+        if constexpr (A::kFloat) {
+            const W* pa = sm1 + pad(tid << 4);
+#pragma unroll
+            for (int i = 0; i < kElems; ++i) r[i] = fp_mulmod(pa[i], r[i], r[i] * K.nq, K.q);
+        } else if constexpr (sizeof(W) == 8) {
+            const u64 mu = __ldg(&Pg->bar_mu);
+            const u32 bs = __ldg(&Pg->bar_shift);
+            const u64* pa = reinterpret_cast<const u64*>(sm1) + pad(tid << 4);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const ulonglong2 va = *reinterpret_cast<const ulonglong2*>(pa + 2 * j);
+                if constexpr (A::kLazy) {
+                    r[2 * j] = barrett_lazy(va.x, r[2 * j], K.nq, mu, bs);
+                    r[2 * j + 1] = barrett_lazy(va.y, r[2 * j + 1], K.nq, mu, bs);
+                } else {
+                    r[2 * j] = barrett_mul(va.x, r[2 * j], K.q, mu, bs);
+                    r[2 * j + 1] = barrett_mul(va.y, r[2 * j + 1], K.q, mu, bs);
+                }
+            }
+        } else {
+            const u64 b64 = __ldg(&Pg->bar64);
+            const W* pa = sm1 + pad(tid << 4);
+#pragma unroll
+            for (int i = 0; i < kElems; ++i) {
+                const u64 z = (u64)pa[i] * r[i];
+                const u64 qh = mulhi64(z, b64);
+                r[i] = csub((W)z + (W)qh * K.nq, K.q);
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the stash was written by generic stores; TMA writes next
+        __syncthreads();                                                // every thread is done with the stash and with sm0
+        if (tid == 0 && next < ntiles) tma_tile_issue(sa, a + ((u64)next << LOGT), kTileBytes, barA);
+        u32 limb_i = s.limb;
+        asm volatile("" : "+r"(limb_i));
+        const LimbParams* __restrict__ Pi = tf.params + limb_i;
+        const LimbK<W> Ki = limb_consts<A>(Pi);
+        slab_inv<A, LOGS, false>(r, sm0, tid, limb_tables(ti, limb_i, logN), s.off, Ki.Ci, Ki.nq, Pi);
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = A::to_raw(r[i]);
+        __syncthreads();   // sm0 is reused by the next trip's forward exchange
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // column kernels (N > 4096): tile = 2^T rows x C columns, T = 12 - LOGC, C = 2^LOGC, row stride 2^S;
 // tile index e = k*C + j  <->  coefficient k*2^S + tile*C + j.  Transform bits of e: [LOGC, 12).
@@ -493,6 +613,35 @@ static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, c
     return cudaGetLastError();
 }
 
+// The persistent form wins where it compiles without spills (32-bit words: k_row_polymul 0.316 -> 0.278 ms at config-4
+// shape); the 64-bit-word policies spill ~40 registers under the 128-register cap and lose 9-13 %.  GFHE_PERSIST=0/1 overrides.
+template <class A>
+static inline bool use_persistent() {
+    static const int env = [] { const char* e = std::getenv("GFHE_PERSIST"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
+    return env < 0 ? sizeof(typename A::word) == 4 : env == 1;
+}
+template <class A, int LOGS, int LOGT>
+static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
+                                              cudaStream_t st) {
+    const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
+    static bool configured[64] = {};
+    static int slots[64] = {};
+    const int dev = pl.device & 63;
+    if (!configured[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(k_row_polymul_persist<A, LOGS, LOGT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        int sms = 148, per_sm = 1;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, pl.device);
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_row_polymul_persist<A, LOGS, LOGT>, TileGeo<LOGT>::NT, smem)) != cudaSuccess) return e;
+        slots[dev] = sms * (per_sm > 0 ? per_sm : 1);
+        configured[dev] = true;
+    }
+    const unsigned grid = nt < (unsigned)slots[dev] ? nt : (unsigned)slots[dev];
+    { ProfScope ps(pl, K_ROW_POLYMUL, st);
+      k_row_polymul_persist<A, LOGS, LOGT><<<grid, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0, nt); }
+    return cudaGetLastError();
+}
+
 // column pass of a forward transform: in0 -> out0 and (if in1) in1 -> out1 in one launch
 template <class A>
 static cudaError_t launch_col_fwd(const Plan& pl, u32 limb0, const u64* in0, u64* out0, const u64* in1, u64* out1, u32 B,
@@ -578,8 +727,10 @@ cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* 
     if (!ws) return cudaErrorInvalidValue;
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, b, ws, B, nt, st)) return e;
-    cudaError_t e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
-                                             : launch_row_polymul<A, 12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
+    cudaError_t e;
+    if (row_stages(pl.logN) == 8 && use_persistent<A>()) e = launch_row_polymul_persist<A, 8, 12>(pl, limb0, c, ws, c, B, nt, st);
+    else e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
+                                      : launch_row_polymul<A, 12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
     if (e != cudaSuccess) return e;
     if ((e = launch_col_inv<A>(pl, limb0, c, c, B, nt, st)) != cudaSuccess) return e;
     return cudaGetLastError();

@@ -51,6 +51,32 @@ struct TileId {
     u32 off;    // offset of the tile inside its polynomial
     u32 limb;
 };
+// ---- L2 prefetch of a later CTA's input ------------------------------------------------------------------------------
+// CTAs are dispatched in blockIdx order and two per SM are resident, so the CTA that takes over this one's slot is about
+// blockIdx.x + 296.  Asking L2 for its input tile now (one instruction, no registers) turns its cold HBM reads at start-up,
+// when it has nothing else to do, into L2 hits.  Measured at config-4 shape (profiles/r01_run11_prefetch.txt):
+//   k_row_polymul  60-bit 0.550 -> 0.531 ms, 50-bit 0.358 -> 0.343 ms   (distance 148 slightly better than 296)
+//   k_row_fwd      30-bit 0.165 -> 0.142 ms, 50-bit -1 %, 60-bit +2 % (so not used by the 60-bit policies)
+//   column kernels +2..15 % slower with a per-line prefetch.global.L2: not used there.
+#ifndef GFHE_PF_MUL
+#define GFHE_PF_MUL 148
+#endif
+#ifndef GFHE_PF_ROW
+#define GFHE_PF_ROW 296
+#endif
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, u32 bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes));
+}
+template <int LOGT, u32 DIST>
+__device__ __forceinline__ void prefetch_row_tile(const u64* base, u32 tid) {
+    if (DIST != 0 && LOGT >= 4 && tid == 0 && blockIdx.x + DIST < gridDim.x)
+        l2_prefetch_bulk(base + ((u64)(blockIdx.x + DIST) << LOGT), (u32)sizeof(u64) << LOGT);
+}
+template <class A> struct RowPf {   // k_row_inv: 30-bit inverse step 0.221 -> 0.207 ms, 50-bit 0.250 -> 0.269 ms (so 32-bit words only)
+    static constexpr u32 kFwd = (sizeof(typename A::word) == 4 || A::kFloat) ? GFHE_PF_ROW : 0;
+    static constexpr u32 kInv = sizeof(typename A::word) == 4 ? GFHE_PF_ROW : 0;
+};
+
 template <int LOGT>
 __device__ __forceinline__ TileId tile_id(u32 logN, u32 B, u32 limb0) {
     TileId s;
@@ -174,6 +200,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
+    prefetch_row_tile<LOGT, RowPf<A>::kFwd>(in, tid);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
     if (A::kFloat && logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words (they differ from canonical ones for the FP64 policy only)
@@ -215,6 +242,7 @@ k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab T = limb_tables(tabs, s.limb, logN);
+    prefetch_row_tile<LOGT, RowPf<A>::kInv>(in, tid);
     W r[kElems];
     if constexpr (LOGT > 4) {
         copy_in_padded<LOGT>(sm, in + s.g0, tid);
@@ -269,6 +297,8 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(u64) << LOGT, mbar);
+    prefetch_row_tile<LOGT, GFHE_PF_MUL>(a, tid);
+    prefetch_row_tile<LOGT, GFHE_PF_MUL>(b, tid);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const TwTab Tf = limb_tables(tf, s.limb, logN);

@@ -15,7 +15,8 @@ wsb = lib.gfhe_poly_mul_workspace_bytes(plan.handle, L, B); ws = torch.empty(wsb
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 def pm(): lib.gfhe_poly_mul(plan.handle, 0, L, B, a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), wsb, st)
 def nt(): lib.gfhe_ntt_forward(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
-for name, f in (("polymul", pm), ("ntt", nt)):
+def it(): lib.gfhe_ntt_inverse(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
+for name, f in (("polymul", pm), ("ntt", nt), ("intt", it)):
     for _ in range(5): f()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -644,12 +644,9 @@ static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, c
 }
 
 // The persistent form wins where it compiles without spills (32-bit words: k_row_polymul 0.316 -> 0.278 ms at config-4
-// shape); the 64-bit-word policies spill ~40 registers under the 128-register cap and lose 9-13 %.  GFHE_PERSIST=0/1 overrides.
+// shape); the 64-bit-word policies spill ~40 registers under the 128-register cap and lose 9-13 %.  GFHE_PERSIST=0/1 (read when the plan is created) overrides.
 template <class A>
-static inline bool use_persistent() {
-    static const int env = [] { const char* e = std::getenv("GFHE_PERSIST"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
-    return env < 0 ? sizeof(typename A::word) == 4 : env == 1;
-}
+static inline bool use_persistent(const Plan& pl) { return pl.persist < 0 ? sizeof(typename A::word) == 4 : pl.persist == 1; }
 template <class A, int LOGS, int LOGT>
 static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
                                               cudaStream_t st) {
@@ -758,7 +755,7 @@ cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* 
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, b, ws, B, nt, st)) return e;
     cudaError_t e;
-    if (row_stages(pl.logN) == 8 && use_persistent<A>()) e = launch_row_polymul_persist<A, 8, 12>(pl, limb0, c, ws, c, B, nt, st);
+    if (row_stages(pl.logN) == 8 && use_persistent<A>(pl)) e = launch_row_polymul_persist<A, 8, 12>(pl, limb0, c, ws, c, B, nt, st);
     else e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false>(pl, limb0, c, ws, c, B, nt, st)
                                       : launch_row_polymul<A, 12, 12, false>(pl, limb0, c, ws, c, B, nt, st);
     if (e != cudaSuccess) return e;

@@ -120,6 +120,7 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     pl->f64 = !pl->w32 && pl->max_bits <= 50 && logN != 0;
     if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->f64 = false;
     if (const char* env = std::getenv("GFHE_NO_F64")) if (env[0] == '1') pl->f64 = false;
+    if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
     const bool f64 = pl->f64;
 
     std::vector<LimbParams> hp(L);

@@ -29,6 +29,7 @@ struct Plan {
     bool f64 = false;                  // every modulus is below 2^50 (and not all below 2^30): the FP64 kernels and FP64-form tables
     bool w32 = false;                  // every modulus is below 2^30: the Shoup32 kernels are used
     bool lazy = false;                 // every modulus is in [2^19, 2^60): the Lazy60 kernels are used
+    int persist = -1;                  // fused row pass: -1 = per-policy default, 0 / 1 = GFHE_PERSIST at plan creation
     LimbParams* d_params = nullptr;    // [L]
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}

@@ -552,6 +552,38 @@ def test_fp64_policy_all_sizes(cuda_device, logn, bits, monkeypatch):
     P.clear_plans()
 
 
+@pytest.mark.parametrize("bits", [30, 50, 60, 61])
+@pytest.mark.parametrize("logn", [13, 16, 17])
+def test_persistent_row_pass_matches_one_tile_per_cta(cuda_device, logn, bits, monkeypatch):
+    """Two-pass products: the persistent fused row pass (TMA prefetch of the next tile, mbarrier phases per trip) and the
+    one-tile-per-CTA kernel give the same words, for every policy, with more tiles than resident CTAs (several trips
+    per CTA, both mbarrier parities) and with fewer; checked against the C oracle at 2^13."""
+    import polynomial as P
+    N, L = 1 << logn, 2
+    B = 40 if logn == 16 else 3          # 2 * 40 * 16 = 1280 tiles: 4-5 trips per resident CTA
+    moduli = P.ntt_primes(bits, L, N=max(N, 1 << 12))
+    a, b = rand_lbn(700 + logn, moduli, B, N), rand_lbn(800 + logn, moduli, B, N)
+    qm1 = np.array(moduli, dtype=np.uint64).reshape(L, 1) - 1
+    a[:, 0, :4] = qm1
+    b[:, 0, :4] = qm1
+    a[:, 1, :] = qm1
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("GFHE_PERSIST", mode)
+        P.clear_plans()
+        with P.ring(moduli):
+            out[mode] = P.poly_mul(ta, tb)
+    monkeypatch.delenv("GFHE_PERSIST")
+    P.clear_plans()
+    assert torch.equal(out["0"], out["1"])
+    with P.ring(moduli):
+        assert torch.equal(P.poly_mul(ta, tb), out["0"])      # the per-policy default
+    if logn == 13:
+        R = oracle_ring(N, moduli)
+        assert np.array_equal(host_u64(out["1"]), R.poly_mul(a, b, fast=True, nthreads=4))
+
+
 def test_empty_and_non_contiguous_operands(cuda_device):
     """Edge cases of the marshalling layer: zero-sized batches come back empty, strided views are made contiguous,
     inputs are never written."""

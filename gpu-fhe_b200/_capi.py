@@ -32,6 +32,10 @@ SYMBOLS = {
     "gfhe_vec_sub": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_mul": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_poly_mul_pre": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
+    "gfhe_ntt_forward_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
+    "gfhe_ntt_inverse_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
+    "gfhe_poly_mul_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp, ctypes.c_size_t, vp]),
+    "gfhe_poly_mul_pre_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
     "gfhe_ntt_mul_acc": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, u32, vp, vp, ctypes.c_uint64, vp, vp]),
     "gfhe_automorphism": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),
@@ -59,7 +63,7 @@ for _name, (_res, _args) in SYMBOLS.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 if lib.gfhe_abi_version() != ABI_VERSION:
     raise ImportError("gpufhe_b200: ABI version mismatch (library %d, binding %d)" % (lib.gfhe_abi_version(), ABI_VERSION))
 

@@ -45,6 +45,7 @@ const char* gfhe_error_string(int code) {
         case GFHE_ENOTABLES: return "plan has no NTT tables (created with log2_n = 0)";
         case GFHE_ETERMS: return "too many terms: terms * q^2 must fit 128 bits";
         case GFHE_EGALOIS: return "Galois element must be odd";
+        case GFHE_ELAYOUT: return "packed 32-bit layout needs every modulus of the plan below 2^30";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown gpufhe_b200 error";
     }
 }
@@ -150,6 +151,50 @@ int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t ba
     if (d_c == d_a || d_c == d_b_ntt) return GFHE_EARG;
     DeviceGuard g(P(plan)->device);
     return (int)launch_poly_mul_pre(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b_ntt, (u64*)d_c, batch, S(stream));
+}
+
+// ---- packed 32-bit layout (every modulus of the plan below 2^30) ----------------------------------------------------
+static int check_packed(const Plan* pl, uint32_t limb0, uint32_t nl) {
+    if (int rc = check_range(pl, limb0, nl)) return rc;
+    if (pl->logN == 0) return GFHE_ENOTABLES;
+    return pl->w32 ? 0 : GFHE_ELAYOUT;
+}
+
+int gfhe_ntt_forward_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                         const uint32_t* d_in, uint32_t* d_out, void* stream) {
+    if (int rc = check_packed(P(plan), limb0, nl)) return rc;
+    if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_ntt_fwd_u32(*P(plan), limb0, nl, d_in, d_out, batch, S(stream));
+}
+
+int gfhe_ntt_inverse_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                         const uint32_t* d_in, uint32_t* d_out, void* stream) {
+    if (int rc = check_packed(P(plan), limb0, nl)) return rc;
+    if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_ntt_inv_u32(*P(plan), limb0, nl, d_in, d_out, batch, S(stream));
+}
+
+int gfhe_poly_mul_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                      const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_c,
+                      void* d_ws, size_t ws_bytes, void* stream) {
+    if (int rc = check_packed(P(plan), limb0, nl)) return rc;
+    if (!d_a || !d_b || !d_c || batch == 0) return GFHE_EARG;
+    if (d_c == d_a || d_c == d_b) return GFHE_EARG;
+    const size_t need = poly_mul_workspace_bytes(*P(plan), nl, batch) / 2;   // one operand-sized scratch of 32-bit words
+    if (need && (!d_ws || ws_bytes < need)) return GFHE_EWORKSPACE;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_poly_mul_u32(*P(plan), limb0, nl, d_a, d_b, d_c, (uint32_t*)d_ws, batch, S(stream));
+}
+
+int gfhe_poly_mul_pre_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                          const uint32_t* d_a, const uint32_t* d_b_ntt, uint32_t* d_c, void* stream) {
+    if (int rc = check_packed(P(plan), limb0, nl)) return rc;
+    if (!d_a || !d_b_ntt || !d_c || batch == 0) return GFHE_EARG;
+    if (d_c == d_a || d_c == d_b_ntt) return GFHE_EARG;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_poly_mul_pre_u32(*P(plan), limb0, nl, d_a, d_b_ntt, d_c, batch, S(stream));
 }
 
 int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner, uint32_t terms,

@@ -200,6 +200,7 @@ __device__ __forceinline__ u32 shoup32(u32 x, u32 w, u32 ws32, u32 nq) {
 //             (the API's layout), but every butterfly is 3 multiply + 4 add/min instructions instead of 9 + 11.
 struct Harvey {
     typedef u64 word;
+    typedef u64 store;   // word type of the [L,B,N] arrays in HBM
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
     __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
@@ -213,6 +214,7 @@ struct Harvey {
 };
 struct Lazy60 {
     typedef u64 word;
+    typedef u64 store;   // word type of the [L,B,N] arrays in HBM
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
     __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
@@ -226,6 +228,7 @@ struct Lazy60 {
 };
 struct Shoup32 {
     typedef u32 word;
+    typedef u64 store;   // word type of the [L,B,N] arrays in HBM
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u32 from_u64(u64 v) { return (u32)v; }
     __device__ static __forceinline__ u64 to_u64(u32 v) { return v; }
@@ -236,6 +239,11 @@ struct Shoup32 {
     static constexpr int kInvC = 2;
     __device__ static __forceinline__ u32 mul(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
     __device__ static __forceinline__ u32 mul_exact(u32 x, u64 w, u64 ws, u32 nq) { return shoup32(x, (u32)w, (u32)(ws >> 32), nq); }
+};
+
+// Shoup32 on arrays of 32-bit words in HBM (int32 / uint32 tensors): half the traffic of the 64-bit layout.
+struct Shoup32P : Shoup32 {
+    typedef u32 store;
 };
 
 // ---- FP64 arithmetic for moduli below 2^50 -----------------------------------------------------------------------
@@ -260,6 +268,7 @@ __device__ __forceinline__ double bits_to_double(u64 b) { return __longlong_as_d
 
 struct Fp50 {
     typedef double word;
+    typedef u64 store;   // word type of the [L,B,N] arrays in HBM
     static constexpr bool kFloat = true;
     static constexpr bool kLazy = false;
     static constexpr int kFwdC = 2;

@@ -18,6 +18,7 @@
 // /root/reference/" polynomial.py":3-5.
 // This file is a template body: ntt_harvey.cu and ntt_lazy.cu include it and instantiate Launcher<A>
 // for one arithmetic policy each (modarith.cuh), so the two sets of kernels compile in parallel.
+#include <atomic>
 #include <cstdlib>
 #include "ntt_core.cuh"
 #include "plan.h"
@@ -67,10 +68,10 @@ struct TileId {
 __device__ __forceinline__ void l2_prefetch_bulk(const void* p, u32 bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes));
 }
-template <int LOGT, u32 DIST>
-__device__ __forceinline__ void prefetch_row_tile(const u64* base, u32 tid) {
+template <int LOGT, u32 DIST, class S>
+__device__ __forceinline__ void prefetch_row_tile(const S* base, u32 tid) {
     if (DIST != 0 && LOGT >= 4 && tid == 0 && blockIdx.x + DIST < gridDim.x)
-        l2_prefetch_bulk(base + ((u64)(blockIdx.x + DIST) << LOGT), (u32)sizeof(u64) << LOGT);
+        l2_prefetch_bulk(base + ((u64)(blockIdx.x + DIST) << LOGT), (u32)sizeof(S) << LOGT);
 }
 template <class A> struct RowPf {   // k_row_inv: 30-bit inverse step 0.221 -> 0.207 ms, 50-bit 0.250 -> 0.269 ms (so 32-bit words only)
     static constexpr u32 kFwd = (sizeof(typename A::word) == 4 || A::kFloat) ? GFHE_PF_ROW : 0;
@@ -176,6 +177,30 @@ __device__ __forceinline__ void copy_in_padded(u32* sm, const u64* in, u32 tid) 
         for (int it = 0; it < 4; ++it) *reinterpret_cast<uint2*>(sm + pad(2u * ((4 * h + it) * NT + tid))) = make_uint2((u32)v[it].x, (u32)v[it].y);
     }
 }
+// 32-bit words in shared memory and in HBM: four residues (one 16-byte global access) never straddle a padded row
+template <int LOGT>
+__device__ __forceinline__ void copy_out_padded(const u32* sm, u32* out, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        const u32 e = 4u * (it * NT + tid);
+        const uint2 lo = *reinterpret_cast<const uint2*>(sm + pad(e)), hi = *reinterpret_cast<const uint2*>(sm + pad(e) + 2);
+        *reinterpret_cast<uint4*>(out + e) = make_uint4(lo.x, lo.y, hi.x, hi.y);
+    }
+}
+template <int LOGT>
+__device__ __forceinline__ void copy_in_padded(u32* sm, const u32* in, u32 tid) {
+    constexpr int NT = TileGeo<LOGT>::NT;
+    uint4 v[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) v[it] = *reinterpret_cast<const uint4*>(in + 4u * (it * NT + tid));
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        u32* d = sm + pad(4u * (it * NT + tid));
+        *reinterpret_cast<uint2*>(d) = make_uint2(v[it].x, v[it].y);
+        *reinterpret_cast<uint2*>(d + 2) = make_uint2(v[it].z, v[it].w);
+    }
+}
 template <int LOGT>
 __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) {
     constexpr int NT = TileGeo<LOGT>::NT;
@@ -192,8 +217,9 @@ __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) 
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
 template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::ROWB)
-k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     typedef typename A::word W;
+    typedef typename A::store S;
     __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
@@ -214,7 +240,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
     fwd_final_all<A>(r, K, Pg);
 #ifdef GFHE_EXP_DIRECTST   // experiment: 16-byte stores straight from the registers (each lane writes its own 128-byte row)
     if constexpr (LOGT > 4) {
-        u64* po = out + s.g0 + (tid << 4);
+        S* po = out + s.g0 + (tid << 4);
 #pragma unroll
         for (int j = 0; j < 8; ++j) *reinterpret_cast<ulonglong2*>(po + 2 * j) = make_ulonglong2(A::to_u64(r[2 * j]), A::to_u64(r[2 * j + 1]));
     } else {
@@ -234,7 +260,7 @@ k_row_fwd(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0
 // tile is the whole polynomial it also folds N^-1 and fully reduces.
 template <class A, int LOGS, int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::ROWB)
-k_row_inv(const u64* in, u64* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     typedef typename A::word W;
     __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
@@ -287,16 +313,18 @@ __device__ __forceinline__ void tma_tile_wait(u64* mbar) {
 // skipped and NTT(a) never leaves the registers -- a third of the butterflies gone for callers that cache NTT(b).
 template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
-k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0) {
+k_row_polymul(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN, u32 B,
+              u32 limb0) {
     typedef typename A::word W;
+    typedef typename A::store S;
     extern __shared__ __align__(16) u64 smem[];
     W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
     W* sm1 = reinterpret_cast<W*>(smem + padded_words(LOGT));      // stash for NTT(a) while NTT(b) is computed
-    u64* smb = smem + 2 * padded_words(LOGT);   // b's tile, fetched by one TMA bulk copy while a is transformed
-    u64* mbar = smb + (1 << LOGT);
+    S* smb = reinterpret_cast<S*>(smem + 2 * padded_words(LOGT));   // b's tile, fetched by one TMA bulk copy while a is transformed
+    u64* mbar = smem + 2 * padded_words(LOGT) + (1 << LOGT);
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
-    if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(u64) << LOGT, mbar);
+    if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(S) << LOGT, mbar);
     prefetch_row_tile<LOGT, GFHE_PF_MUL>(a, tid);
     prefetch_row_tile<LOGT, GFHE_PF_MUL>(b, tid);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
@@ -313,7 +341,7 @@ k_row_polymul(const u64* a, const u64* b, u64* c, const Tables tf, const Tables 
     fwd_semi_all<A>(r, K, Pg);
     if constexpr (BNTT) {
         tma_tile_wait(mbar);
-        const u64* pb = smb + (tid << 4);   // this thread's 16 residues of NTT(b), same positions as r[]
+        const S* pb = smb + (tid << 4);   // this thread's 16 residues of NTT(b), same positions as r[]
         if constexpr (A::kFloat) {
 #pragma unroll
             for (int i = 0; i < kElems; ++i) {
@@ -413,17 +441,19 @@ __device__ __forceinline__ void mbar_wait(u64* mbar, u32 parity) {
 
 template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
-k_row_polymul_persist(const u64* a, const u64* b, u64* c, const Tables tf, const Tables ti, u32 logN, u32 B, u32 limb0, u32 ntiles) {
+k_row_polymul_persist(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN,
+                      u32 B, u32 limb0, u32 ntiles) {
     typedef typename A::word W;
+    typedef typename A::store S;
     extern __shared__ __align__(16) u64 smem[];
     W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
-    u64* sa = smem + padded_words(LOGT);                           // a's landing buffer (linear u64), then the stash of NTT(a)
+    S* sa = reinterpret_cast<S*>(smem + padded_words(LOGT));       // a's landing buffer (linear), then the stash of NTT(a)
     W* sm1 = reinterpret_cast<W*>(sa);
-    u64* smb = smem + 2 * padded_words(LOGT);                      // b's landing buffer
-    u64* barA = smb + (1 << LOGT);
+    S* smb = reinterpret_cast<S*>(smem + 2 * padded_words(LOGT));  // b's landing buffer
+    u64* barA = smem + 2 * padded_words(LOGT) + (1 << LOGT);
     u64* barB = barA + 1;
     const u32 tid = threadIdx.x;
-    constexpr u32 kTileBytes = (u32)sizeof(u64) << LOGT;
+    constexpr u32 kTileBytes = (u32)sizeof(S) << LOGT;
     constexpr int P0 = Sched<LOGS>::p0(0);
     if (tid == 0) {
         mbar_init(barA); mbar_init(barB);
@@ -539,20 +569,22 @@ template <class A, int LOGC, int S>
 #define GFHE_COLB 4   // 64 registers: four resident CTAs per SM (measured: k_col_fwd -2.7 %, k_col_inv -8.7 % against 2 -> 3 resident)
 #endif
 __global__ void __launch_bounds__(256, GFHE_COLB)
-k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tabs, u32 B, u32 limb0) {
+k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename A::store* in1, typename A::store* out1, const Tables tabs,
+          u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
     typedef typename A::word W;
+    typedef typename A::store St;
     __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
-    const u64* in = (blockIdx.y ? in1 : in0) + id.base;
-    u64* out = (blockIdx.y ? out1 : out0) + id.base;
+    const St* in = (blockIdx.y ? in1 : in0) + id.base;
+    St* out = (blockIdx.y ? out1 : out0) + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     __shared__ ulonglong2 tws[256];
     W r[kElems];
     {
-        const u64* p = in + Geo::template toff<8>(tid);
+        const St* p = in + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
@@ -564,11 +596,11 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
         GFHE_SYNC();
         sm_load<4>(sm, tid, r);
         fwd_round<A, 3, Geo::LO4, TwSm, fwd_bound(1, 4 - Geo::LO8)>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
-        u64* p = out + Geo::template toff<4>(tid);
+        St* p = out + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = A::to_raw(r[i]);
     } else {
-        u64* p = out + Geo::template toff<8>(tid);
+        St* p = out + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_raw(r[i]);
     }
@@ -576,24 +608,25 @@ k_col_fwd(const u64* in0, u64* out0, const u64* in1, u64* out1, const Tables tab
 
 template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, GFHE_COLB)
-k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
+k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables tabs, u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
     typedef typename A::word W;
+    typedef typename A::store St;
     __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
     const u32 tid = threadIdx.x;
     const ColId id = col_id<LOGC, S>(B, limb0);
-    const u64* in = in0 + id.base;
-    u64* out = out0 + id.base;
+    const St* in = in0 + id.base;
+    St* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     __shared__ ulonglong2 tws[256];
     W r[kElems];
     if constexpr (Geo::TWO) {
-        const u64* p = in + Geo::template toff<4>(tid);
+        const St* p = in + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<4>(i)], tid * 77u + i);
     } else {
-        const u64* p = in + Geo::template toff<8>(tid);
+        const St* p = in + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
@@ -606,7 +639,7 @@ k_col_inv(const u64* in0, u64* out0, const Tables tabs, u32 B, u32 limb0) {
         sm_load<8>(sm, tid, r);
     }
     inv_round<A, 3, Geo::LO8, true>(r, TwSm{tws, 1u}, K.Ci, K.nq, Pg);
-    u64* p = out + Geo::template toff<8>(tid);
+    St* p = out + Geo::template toff<8>(tid);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_u64(r[i]);
 }
@@ -629,7 +662,7 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
 }
 
 template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
-static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
+static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const typename A::store* a, const typename A::store* b, typename A::store* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
     const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
     static bool configured[64] = {};   // per template instantiation, per device
@@ -648,22 +681,22 @@ static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const u64* a, c
 template <class A>
 static inline bool use_persistent(const Plan& pl) { return pl.persist < 0 ? sizeof(typename A::word) == 4 : pl.persist == 1; }
 template <class A, int LOGS, int LOGT>
-static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const u64* a, const u64* b, u64* c, u32 B, unsigned nt,
+static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const typename A::store* a, const typename A::store* b, typename A::store* c, u32 B, unsigned nt,
                                               cudaStream_t st) {
     const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
-    static bool configured[64] = {};
-    static int slots[64] = {};
+    static std::atomic<int> slots[64];   // resident CTAs per device, 0 = not configured yet (per template instantiation)
     const int dev = pl.device & 63;
-    if (!configured[dev]) {
+    int nslots = slots[dev].load(std::memory_order_acquire);
+    if (nslots == 0) {
         cudaError_t e = cudaFuncSetAttribute(k_row_polymul_persist<A, LOGS, LOGT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         int sms = 148, per_sm = 1;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, pl.device);
         if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_row_polymul_persist<A, LOGS, LOGT>, TileGeo<LOGT>::NT, smem)) != cudaSuccess) return e;
-        slots[dev] = sms * (per_sm > 0 ? per_sm : 1);
-        configured[dev] = true;
+        nslots = sms * (per_sm > 0 ? per_sm : 1);
+        slots[dev].store(nslots, std::memory_order_release);
     }
-    const unsigned grid = nt < (unsigned)slots[dev] ? nt : (unsigned)slots[dev];
+    const unsigned grid = nt < (unsigned)nslots ? nt : (unsigned)nslots;
     { ProfScope ps(pl, K_ROW_POLYMUL, st);
       k_row_polymul_persist<A, LOGS, LOGT><<<grid, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0, nt); }
     return cudaGetLastError();
@@ -671,7 +704,8 @@ static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const u
 
 // column pass of a forward transform: in0 -> out0 and (if in1) in1 -> out1 in one launch
 template <class A>
-static cudaError_t launch_col_fwd(const Plan& pl, u32 limb0, const u64* in0, u64* out0, const u64* in1, u64* out1, u32 B,
+static cudaError_t launch_col_fwd(const Plan& pl, u32 limb0, const typename A::store* in0, typename A::store* out0, const typename A::store* in1,
+                                  typename A::store* out1, u32 B,
                                   unsigned nt, cudaStream_t st) {
     const u32 S = row_stages(pl.logN);
     const dim3 grid(nt, in1 ? 2 : 1);
@@ -686,7 +720,7 @@ static cudaError_t launch_col_fwd(const Plan& pl, u32 limb0, const u64* in0, u64
     return cudaSuccess;
 }
 template <class A>
-static cudaError_t launch_col_inv(const Plan& pl, u32 limb0, const u64* in, u64* out, u32 B, unsigned nt, cudaStream_t st) {
+static cudaError_t launch_col_inv(const Plan& pl, u32 limb0, const typename A::store* in, typename A::store* out, u32 B, unsigned nt, cudaStream_t st) {
     const u32 S = row_stages(pl.logN);
     ProfScope ps(pl, K_COL_INV, st);
     switch ((12 - (int)(pl.logN - S)) * 16 + (int)S) {
@@ -700,7 +734,7 @@ static cudaError_t launch_col_inv(const Plan& pl, u32 limb0, const u64* in, u64*
 }
 
 template <class A>
-cudaError_t Launcher<A>::ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+cudaError_t Launcher<A>::ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const typename A::store* in, typename A::store* out, u32 B, cudaStream_t st) {
     const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
@@ -719,7 +753,7 @@ cudaError_t Launcher<A>::ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* i
 }
 
 template <class A>
-cudaError_t Launcher<A>::ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+cudaError_t Launcher<A>::ntt_inv(const Plan& pl, u32 limb0, u32 nl, const typename A::store* in, typename A::store* out, u32 B, cudaStream_t st) {
     const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
         switch (pl.logN) {
@@ -740,7 +774,7 @@ cudaError_t Launcher<A>::ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* i
 }
 
 template <class A>
-cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
+cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const typename A::store* a, const typename A::store* b, typename A::store* c, typename A::store* ws, u32 B,
                                   cudaStream_t st) {
     const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {
@@ -764,7 +798,7 @@ cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* 
 }
 
 template <class A>
-cudaError_t Launcher<A>::poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B,
+cudaError_t Launcher<A>::poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const typename A::store* a, const typename A::store* b_ntt, typename A::store* c, u32 B,
                                       cudaStream_t st) {
     const unsigned nt = tiles_of(pl, nl, B);
     if (pl.logN <= (u32)kMaxLogSlab) {

@@ -169,6 +169,7 @@ extern template struct Launcher<Harvey>;
 extern template struct Launcher<Lazy60>;
 extern template struct Launcher<Shoup32>;
 extern template struct Launcher<Fp50>;
+extern template struct Launcher<Shoup32P>;
 
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::ntt_fwd(pl, limb0, nl, in, out, B, st);
@@ -191,6 +192,19 @@ cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a,
     if (pl.f64) return Launcher<Fp50>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st)
                    : Launcher<Harvey>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
+}
+// packed layout: only plans on the 32-bit policy have it (every modulus below 2^30)
+cudaError_t launch_ntt_fwd_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
+    return pl.w32 ? Launcher<Shoup32P>::ntt_fwd(pl, limb0, nl, in, out, B, st) : cudaErrorNotSupported;
+}
+cudaError_t launch_ntt_inv_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
+    return pl.w32 ? Launcher<Shoup32P>::ntt_inv(pl, limb0, nl, in, out, B, st) : cudaErrorNotSupported;
+}
+cudaError_t launch_poly_mul_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b, u32* c, u32* ws, u32 B, cudaStream_t st) {
+    return pl.w32 ? Launcher<Shoup32P>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st) : cudaErrorNotSupported;
+}
+cudaError_t launch_poly_mul_pre_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b_ntt, u32* c, u32 B, cudaStream_t st) {
+    return pl.w32 ? Launcher<Shoup32P>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st) : cudaErrorNotSupported;
 }
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
     if (pl.logN <= 12) return 0;

@@ -58,12 +58,11 @@ int plan_destroy(Plan* p);
 // ntt_kernels.inl, instantiated per arithmetic policy by ntt_harvey.cu / ntt_lazy.cu
 template <class A>
 struct Launcher {
-    static cudaError_t ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
-    static cudaError_t ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st);
-    static cudaError_t poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B,
-                                cudaStream_t st);
-    static cudaError_t poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B,
-                                    cudaStream_t st);
+    typedef typename A::store S;   // word type of the arrays in HBM (u64; u32 for the packed 32-bit layout)
+    static cudaError_t ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const S* in, S* out, u32 B, cudaStream_t st);
+    static cudaError_t ntt_inv(const Plan& pl, u32 limb0, u32 nl, const S* in, S* out, u32 B, cudaStream_t st);
+    static cudaError_t poly_mul(const Plan& pl, u32 limb0, u32 nl, const S* a, const S* b, S* c, S* ws, u32 B, cudaStream_t st);
+    static cudaError_t poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const S* a, const S* b_ntt, S* c, u32 B, cudaStream_t st);
 };
 
 // plan.cu -- pick the policy of the plan; all operate on limbs [limb0, limb0 + nl), buffers are [nl, B, N]
@@ -73,6 +72,11 @@ cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, con
                             cudaStream_t st);
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B);
 cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st);
+// packed 32-bit layout (plans whose moduli are all below 2^30): the same operations on arrays of 32-bit words
+cudaError_t launch_ntt_fwd_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st);
+cudaError_t launch_ntt_inv_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st);
+cudaError_t launch_poly_mul_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b, u32* c, u32* ws, u32 B, cudaStream_t st);
+cudaError_t launch_poly_mul_pre_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b_ntt, u32* c, u32 B, cudaStream_t st);
 
 // vec_kernels.cu
 cudaError_t launch_vec_op(int op, const Plan& pl, u32 limb0, u32 nl, const long long* a, const long long* b,

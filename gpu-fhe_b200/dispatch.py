@@ -17,6 +17,7 @@ from . import _capi, ring
 
 _VEC_FN = {0: "gfhe_vec_add", 1: "gfhe_vec_sub", 2: "gfhe_vec_mul"}
 _INT_DTYPES = (torch.int64, torch.uint64)
+_PACKED_DTYPES = (torch.int32, torch.uint32)   # packed layout: CUDA tensors of 32-bit words, moduli below 2^30 only
 
 
 def _require_cuda() -> None:
@@ -38,9 +39,12 @@ class _Arg:
     def __init__(self, x, device: Optional[torch.device] = None):
         self.kind = "cuda"
         self.np_dtype = None
+        self.packed = False
         if isinstance(x, torch.Tensor):
-            if x.dtype not in _INT_DTYPES:
-                raise TypeError("expected an int64/uint64 tensor of residues, got %s" % x.dtype)
+            if x.dtype in _PACKED_DTYPES:
+                self.packed = True
+            elif x.dtype not in _INT_DTYPES:
+                raise TypeError("expected an int64/uint64 (or packed int32/uint32) tensor of residues, got %s" % x.dtype)
             if x.is_cuda:
                 self.t = x.contiguous()
             else:
@@ -107,6 +111,7 @@ def _vec_moduli(MOD, shape: Tuple[int, ...]) -> Tuple[Tuple[int, ...], int]:
 def vec_op(op: int, a, b, MOD):
     A = _Arg(a)
     B = _Arg(b, A.t.device)
+    _no_packed(A, B)
     if B.t.device != A.t.device:
         raise ValueError("operands live on different devices")
     moduli, inner = _vec_moduli(MOD, A.shape)
@@ -121,6 +126,17 @@ def vec_op(op: int, a, b, MOD):
 
 
 # ---- transforms (/root/reference/arithmetic.py:15-19) and product -----------------------------------
+
+def _same_layout(a: "_Arg", b: "_Arg") -> None:
+    if a.packed != b.packed:
+        raise TypeError("operands must use the same word size (both 64-bit or both packed 32-bit)")
+
+
+def _no_packed(*args: "_Arg") -> None:
+    for a in args:
+        if a.packed:
+            raise TypeError("this operation has no packed 32-bit form yet: pass int64/uint64 residues")
+
 
 def _lbn(shape: Sequence[int], L: int) -> Tuple[int, int, int]:
     """Map an operand shape (..., N) onto the canonical [L, B, N]."""
@@ -147,7 +163,10 @@ def ntt(x, MOD, inverse: bool):
     out = torch.empty_like(X.t)
     if B == 0:
         return X.wrap(out)
-    fn = _capi.lib.gfhe_ntt_inverse if inverse else _capi.lib.gfhe_ntt_forward
+    if X.packed:
+        fn = _capi.lib.gfhe_ntt_inverse_u32 if inverse else _capi.lib.gfhe_ntt_forward_u32
+    else:
+        fn = _capi.lib.gfhe_ntt_inverse if inverse else _capi.lib.gfhe_ntt_forward
     _capi.check(fn(plan.handle, 0, L, B, _ptr(X.t), _ptr(out), _stream(dev)), "gfhe_ntt")
     return X.wrap(out)
 
@@ -164,9 +183,11 @@ def poly_mul(a, b, MOD):
     out = torch.empty_like(A.t)
     if B == 0:
         return A.wrap(out)
-    ws_bytes = _capi.lib.gfhe_poly_mul_workspace_bytes(plan.handle, L, B)
+    _same_layout(A, Bv)
+    ws_bytes = _capi.lib.gfhe_poly_mul_workspace_bytes(plan.handle, L, B) // (2 if A.packed else 1)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev) if ws_bytes else None
-    _capi.check(_capi.lib.gfhe_poly_mul(plan.handle, 0, L, B, _ptr(A.t), _ptr(Bv.t), _ptr(out),
+    fn = _capi.lib.gfhe_poly_mul_u32 if A.packed else _capi.lib.gfhe_poly_mul
+    _capi.check(fn(plan.handle, 0, L, B, _ptr(A.t), _ptr(Bv.t), _ptr(out),
                                         _ptr(ws) if ws is not None else None, ws_bytes, _stream(dev)), "gfhe_poly_mul")
     return A.wrap(out)
 
@@ -184,8 +205,9 @@ def poly_mul_pre(a, b_ntt, MOD):
     out = torch.empty_like(A.t)
     if B == 0:
         return A.wrap(out)
-    _capi.check(_capi.lib.gfhe_poly_mul_pre(plan.handle, 0, L, B, _ptr(A.t), _ptr(Bv.t), _ptr(out), _stream(dev)),
-                "gfhe_poly_mul_pre")
+    _same_layout(A, Bv)
+    fn = _capi.lib.gfhe_poly_mul_pre_u32 if A.packed else _capi.lib.gfhe_poly_mul_pre
+    _capi.check(fn(plan.handle, 0, L, B, _ptr(A.t), _ptr(Bv.t), _ptr(out), _stream(dev)), "gfhe_poly_mul_pre")
     return A.wrap(out)
 
 
@@ -201,6 +223,7 @@ def mul_acc(a, b, MOD, stacked: bool):
         b = torch.stack([_Arg(x).t for x in b]) if not isinstance(b[0], np.ndarray) else np.stack(b)
     A = _Arg(a)
     Bv = _Arg(b, A.t.device)
+    _no_packed(A, Bv)
     if A.shape != Bv.shape:
         raise AssertionError("operands must have equal shapes")
     L = len(moduli)
@@ -227,6 +250,7 @@ def automorphism(x, k: int, MOD, ntt_domain: bool):
     """a(X) -> a(X^k), k odd, on every limb-polynomial of x ([L, B, N]); out of place."""
     moduli = ring.resolve_moduli(MOD)
     X = _Arg(x)
+    _no_packed(X)
     L, B, N = _lbn(X.shape, len(moduli))
     k = int(k) % (2 * N)
     if k % 2 == 0:

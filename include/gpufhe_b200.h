@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define GFHE_ABI_VERSION 2
+#define GFHE_ABI_VERSION 3
 
 #define GFHE_EARG      (-1)   /* null pointer / zero size */
 #define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
@@ -51,6 +51,7 @@ extern "C" {
 #define GFHE_ENOTABLES (-9)   /* plan was created without NTT tables (log2_n == 0) */
 #define GFHE_ETERMS    (-10)  /* too many terms: terms * q^2 must fit 128 bits */
 #define GFHE_EGALOIS   (-11)  /* Galois element must be odd */
+#define GFHE_ELAYOUT   (-12)  /* packed 32-bit layout asked of a plan with a modulus >= 2^30 */
 
 typedef struct gfhe_plan* gfhe_plan_t;   /* opaque; one per (device, N, modulus chain) */
 
@@ -85,6 +86,20 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t
  * polynomials by one cached operand.  No workspace.  c may alias neither input. */
 int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
                       const uint64_t* d_a, const uint64_t* d_b_ntt, uint64_t* d_c, void* stream);
+
+/* Packed 32-bit layout: the same four operations on [num_limbs, batch, N] arrays of 32-bit words (int32 / uint32
+ * tensors), for plans whose moduli are ALL below 2^30 (GFHE_ELAYOUT otherwise) -- the north-star's "32-bit where the
+ * moduli fit".  Half the HBM traffic of the 64-bit layout; results are the same residues.  The poly-mul workspace is
+ * gfhe_poly_mul_workspace_bytes() / 2. */
+int gfhe_ntt_forward_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                         const uint32_t* d_in, uint32_t* d_out, void* stream);
+int gfhe_ntt_inverse_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                         const uint32_t* d_in, uint32_t* d_out, void* stream);
+int gfhe_poly_mul_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                      const uint32_t* d_a, const uint32_t* d_b, uint32_t* d_c,
+                      void* d_workspace, size_t workspace_bytes, void* stream);
+int gfhe_poly_mul_pre_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                          const uint32_t* d_a, const uint32_t* d_b_ntt, uint32_t* d_c, void* stream);
 
 /* out = (a op b) mod q_l, exact for ANY int64 inputs (Python % semantics, result in [0, q)).
  * Buffers are [num_limbs, inner]; limb l of the range uses modulus limb0 + l. */

@@ -584,6 +584,57 @@ def test_persistent_row_pass_matches_one_tile_per_cta(cuda_device, logn, bits, m
         assert np.array_equal(host_u64(out["1"]), R.poly_mul(a, b, fast=True, nthreads=4))
 
 
+# ---------------------------------------------------------------------------------------------------
+# packed 32-bit layout (int32 / uint32 tensors, every modulus below 2^30): same residues as the 64-bit layout
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("logn", [4, 5, 8, 10, 12, 13, 14, 16, 17, 18])
+def test_packed_u32_layout_all_sizes(cuda_device, logn):
+    import polynomial as P
+    N, L = 1 << logn, 2
+    moduli = P.ntt_primes(30, L, N=max(N, 1 << 12))
+    B = 40 if logn == 16 else (3 if logn < 16 else 1)      # 2^16: several trips of the persistent row pass
+    a, b = rand_lbn(900 + logn, moduli, B, N), rand_lbn(950 + logn, moduli, B, N)
+    qm1 = np.array(moduli, dtype=np.uint64).reshape(L, 1) - 1
+    a[:, 0, :4] = qm1
+    b[:, 0, :4] = qm1
+    a[:, 0, 4] = 0
+    ta, tb = dev_i64(a, cuda_device), dev_i64(b, cuda_device)
+    pa, pb = ta.to(torch.int32), tb.to(torch.int32)
+    with P.ring(moduli):
+        X64, c64 = P.NTT(ta), P.poly_mul(ta, tb)
+        X, c = P.NTT(pa), P.poly_mul(pa, pb)
+        back = P.iNTT(X)
+        pre = P.poly_mul_pre(pa, P.NTT(pb))
+    assert X.dtype == c.dtype == back.dtype == torch.int32 and X.shape == pa.shape
+    assert torch.equal(X.to(torch.int64), X64)
+    assert torch.equal(c.to(torch.int64), c64)
+    assert torch.equal(back, pa) and torch.equal(pre, c)
+    assert torch.equal(pa, ta.to(torch.int32)) and torch.equal(pb, tb.to(torch.int32))       # inputs untouched
+    if logn <= 14:
+        R = oracle_ring(N, moduli)
+        assert np.array_equal(X.to(torch.int64).cpu().numpy().view(np.uint64), R.ntt(a, fast=True, nthreads=4))
+        assert np.array_equal(c.to(torch.int64).cpu().numpy().view(np.uint64), R.poly_mul(a, b, fast=True, nthreads=4))
+
+
+def test_packed_u32_layout_errors(cuda_device):
+    import polynomial as P
+    from gpu_fhe_b200 import _capi
+    N = 256
+    x = torch.zeros((2, 1, N), dtype=torch.int32, device=cuda_device)
+    with P.ring(P.ntt_primes(50, 2)):
+        with pytest.raises(_capi.GpuFheError) as e:
+            P.NTT(x)
+        assert e.value.code == -12                                   # GFHE_ELAYOUT: a modulus does not fit 30 bits
+    m30 = P.ntt_primes(30, 2)
+    with P.ring(m30):
+        with pytest.raises(TypeError):
+            P.poly_mul(x, x.to(torch.int64))                         # mixed word sizes
+        with pytest.raises(TypeError):
+            P.automorphism(x, 5)                                     # no packed form yet
+    with pytest.raises(TypeError):
+        P.vec_add(x, x, np.array(m30, dtype=np.int64).reshape(2, 1, 1))
+
+
 def test_empty_and_non_contiguous_operands(cuda_device):
     """Edge cases of the marshalling layer: zero-sized batches come back empty, strided views are made contiguous,
     inputs are never written."""

@@ -31,6 +31,9 @@ namespace gfhe {
 #ifndef GFHE_ROWB
 #define GFHE_ROWB 2
 #endif
+#ifndef GFHE_MINB32
+#define GFHE_MINB32 3   // 32-bit words, where three CTAs fit in shared memory
+#endif
 #ifndef GFHE_MINB
 #define GFHE_MINB 2   // resident 256-thread CTAs per SM the 4096-residue kernels are compiled for (128 registers)
 #endif
@@ -40,6 +43,14 @@ struct TileGeo {
     static constexpr int MINB = LOGT == 12 ? GFHE_MINB : 1;   // 256-thread CTAs: cap at 128 registers (fused poly-mul kernel)
     static constexpr int ROWB = LOGT == 12 ? GFHE_ROWB : 1;   // stand-alone row passes
 };
+
+// resident CTAs per SM the stand-alone row passes are compiled for.  32-bit words need half the registers; four resident
+// CTAs pay on the packed layout (2^16 NTT 0.200 -> 0.177 ms) and not on the 64-bit one, which is DRAM-bound (0.226 -> 0.229)
+#ifndef GFHE_ROWB32
+#define GFHE_ROWB32 4
+#endif
+template <class A, int LOGT>
+struct RowOcc { static constexpr int kB = LOGT == 12 ? (sizeof(typename A::store) == 4 ? GFHE_ROWB32 : GFHE_ROWB) : 1; };
 
 struct Tables {   // kernel argument: the plan's device tables
     const ulonglong2* tw;    // [L][N]
@@ -216,7 +227,7 @@ __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) 
 
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
 template <class A, int LOGS, int LOGT>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::ROWB)
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
 k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     typedef typename A::word W;
     typedef typename A::store S;
@@ -259,7 +270,7 @@ k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs
 // Inverse: the LOGS low stages (bottom first).  Always the first pass of an inverse NTT; when the
 // tile is the whole polynomial it also folds N^-1 and fully reduces.
 template <class A, int LOGS, int LOGT, bool WHOLE>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::ROWB)
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
 k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
     typedef typename A::word W;
     __shared__ __align__(16) W sm[padded_words(LOGT)];
@@ -287,6 +298,22 @@ k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs
 // ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 // one thread: arm the barrier with the byte count and start the copy
+// Shared-memory layout of the fused poly-mul kernels, in bytes: exchange buffer | stash of NTT(a) (the persistent form
+// also lands the next a tile there, linear, in storage words) | b's landing buffer | two mbarriers.
+template <class A, int LOGT, bool PERSIST>
+struct MulSmem {
+    typedef typename A::word W;
+    typedef typename A::store S;
+    static constexpr u32 kExch = ((u32)sizeof(W) * padded_words(LOGT) + 15u) & ~15u;
+    static constexpr u32 kTile = (u32)sizeof(S) << LOGT;
+    static constexpr u32 kStash = (PERSIST && kTile > kExch) ? kTile : kExch;
+    static constexpr u32 kOff1 = kExch, kOffB = kExch + kStash, kOffBar = kOffB + kTile, kBytes = kOffBar + 16;
+    static_assert(kOff1 % 16 == 0 && kOffB % 16 == 0 && kOffBar % 8 == 0, "TMA destinations are 16-byte aligned");
+    // resident CTAs per SM the kernel is compiled for: three when shared memory (227 KB) and 80 registers allow
+    static constexpr int kFit = (int)((227u * 1024u) / (kBytes + 1024u));
+    static constexpr int kMinB = LOGT == 12 ? ((sizeof(W) == 4 && kFit >= 3) ? (kFit < GFHE_MINB32 ? kFit : GFHE_MINB32) : GFHE_MINB) : 1;
+};
+
 __device__ __forceinline__ void tma_tile_load(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
     const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
@@ -312,16 +339,17 @@ __device__ __forceinline__ void tma_tile_wait(u64* mbar) {
 // BNTT: b is already in the NTT domain (canonical residues, the order gfhe_ntt_forward writes): its forward transform is
 // skipped and NTT(a) never leaves the registers -- a third of the butterflies gone for callers that cache NTT(b).
 template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, MulSmem<A, LOGT, false>::kMinB)
 k_row_polymul(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN, u32 B,
               u32 limb0) {
     typedef typename A::word W;
     typedef typename A::store S;
-    extern __shared__ __align__(16) u64 smem[];
+    using Lay = MulSmem<A, LOGT, false>;
+    extern __shared__ __align__(16) unsigned char smem[];
     W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
-    W* sm1 = reinterpret_cast<W*>(smem + padded_words(LOGT));      // stash for NTT(a) while NTT(b) is computed
-    S* smb = reinterpret_cast<S*>(smem + 2 * padded_words(LOGT));   // b's tile, fetched by one TMA bulk copy while a is transformed
-    u64* mbar = smem + 2 * padded_words(LOGT) + (1 << LOGT);
+    W* sm1 = reinterpret_cast<W*>(smem + Lay::kOff1);              // stash for NTT(a) while NTT(b) is computed
+    S* smb = reinterpret_cast<S*>(smem + Lay::kOffB);              // b's tile, fetched by one TMA bulk copy while a is transformed
+    u64* mbar = reinterpret_cast<u64*>(smem + Lay::kOffBar);
     const u32 tid = threadIdx.x;
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(S) << LOGT, mbar);
@@ -440,17 +468,18 @@ __device__ __forceinline__ void mbar_wait(u64* mbar, u32 parity) {
 }
 
 template <class A, int LOGS, int LOGT>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, TileGeo<LOGT>::MINB)
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, MulSmem<A, LOGT, true>::kMinB)
 k_row_polymul_persist(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN,
                       u32 B, u32 limb0, u32 ntiles) {
     typedef typename A::word W;
     typedef typename A::store S;
-    extern __shared__ __align__(16) u64 smem[];
+    using Lay = MulSmem<A, LOGT, true>;
+    extern __shared__ __align__(16) unsigned char smem[];
     W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
-    S* sa = reinterpret_cast<S*>(smem + padded_words(LOGT));       // a's landing buffer (linear), then the stash of NTT(a)
+    S* sa = reinterpret_cast<S*>(smem + Lay::kOff1);               // a's landing buffer (linear), then the stash of NTT(a)
     W* sm1 = reinterpret_cast<W*>(sa);
-    S* smb = reinterpret_cast<S*>(smem + 2 * padded_words(LOGT));  // b's landing buffer
-    u64* barA = smem + 2 * padded_words(LOGT) + (1 << LOGT);
+    S* smb = reinterpret_cast<S*>(smem + Lay::kOffB);              // b's landing buffer
+    u64* barA = reinterpret_cast<u64*>(smem + Lay::kOffBar);
     u64* barB = barA + 1;
     const u32 tid = threadIdx.x;
     constexpr u32 kTileBytes = (u32)sizeof(S) << LOGT;
@@ -664,7 +693,7 @@ static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
 template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const typename A::store* a, const typename A::store* b, typename A::store* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
-    const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
+    const size_t smem = MulSmem<A, LOGT, false>::kBytes;
     static bool configured[64] = {};   // per template instantiation, per device
     const int dev = pl.device & 63;
     if (!configured[dev] && smem > 48 * 1024) {
@@ -683,7 +712,7 @@ static inline bool use_persistent(const Plan& pl) { return pl.persist < 0 ? size
 template <class A, int LOGS, int LOGT>
 static cudaError_t launch_row_polymul_persist(const Plan& pl, u32 limb0, const typename A::store* a, const typename A::store* b, typename A::store* c, u32 B, unsigned nt,
                                               cudaStream_t st) {
-    const size_t smem = sizeof(u64) * ((size_t)2 * padded_words(LOGT) + ((size_t)1 << LOGT) + 2);
+    const size_t smem = MulSmem<A, LOGT, true>::kBytes;
     static std::atomic<int> slots[64];   // resident CTAs per device, 0 = not configured yet (per template instantiation)
     const int dev = pl.device & 63;
     int nslots = slots[dev].load(std::memory_order_acquire);

@@ -201,6 +201,7 @@ __device__ __forceinline__ u32 shoup32(u32 x, u32 w, u32 ws32, u32 nq) {
 struct Harvey {
     typedef u64 word;
     typedef u64 store;   // word type of the [L,B,N] arrays in HBM
+    typedef ulonglong2 tw_t;    // twiddle-table entry
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
     __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
@@ -215,6 +216,7 @@ struct Harvey {
 struct Lazy60 {
     typedef u64 word;
     typedef u64 store;   // word type of the [L,B,N] arrays in HBM
+    typedef ulonglong2 tw_t;    // twiddle-table entry
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u64 from_u64(u64 v) { return v; }
     __device__ static __forceinline__ u64 to_u64(u64 v) { return v; }
@@ -229,6 +231,7 @@ struct Lazy60 {
 struct Shoup32 {
     typedef u32 word;
     typedef u64 store;   // word type of the [L,B,N] arrays in HBM
+    typedef u64 tw_t;    // twiddle-table entry (compact: w | w' << 32)
     static constexpr bool kFloat = false;
     __device__ static __forceinline__ u32 from_u64(u64 v) { return (u32)v; }
     __device__ static __forceinline__ u64 to_u64(u32 v) { return v; }
@@ -269,6 +272,7 @@ __device__ __forceinline__ double bits_to_double(u64 b) { return __longlong_as_d
 struct Fp50 {
     typedef double word;
     typedef u64 store;   // word type of the [L,B,N] arrays in HBM
+    typedef ulonglong2 tw_t;    // twiddle-table entry
     static constexpr bool kFloat = true;
     static constexpr bool kLazy = false;
     static constexpr int kFwdC = 2;

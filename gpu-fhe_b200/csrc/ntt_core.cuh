@@ -64,6 +64,17 @@ __device__ __forceinline__ ulonglong2 ldg_tw(const ulonglong2* p) {
     asm volatile("ld.global.nc.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
     return v;
 }
+// Compact 8-byte entry of the 32-bit policies: w | (w' << 32), w' = floor(w * 2^32 / q) = the high word of the 64-bit
+// Shoup constant.  Returned in the positions Shoup32::mul reads ((u32)x and (u32)(y >> 32)): no instructions.
+// The row passes read 240 bytes of 16-byte twiddles per thread against 128 bytes of data, all through L2 (tables of a
+// 32-limb plan are 64 MB, re-read by every polynomial of the batch); with 32-bit words that is what bounds them.
+__device__ __forceinline__ ulonglong2 tw_expand(ulonglong2 v) { return v; }
+__device__ __forceinline__ ulonglong2 tw_expand(u64 e) { return make_ulonglong2(e & 0xffffffffull, e & 0xffffffff00000000ull); }
+__device__ __forceinline__ ulonglong2 ldg_tw(const u64* p) {
+    u64 e;
+    asm volatile("ld.global.nc.u64 %0, [%1];" : "=l"(e) : "l"(p));
+    return tw_expand(e);
+}
 
 // Where a round's twiddles come from.
 //  Std : the bit-reversed table tw[k] = psi^brv(k); local bit b, sub-group hi reads tw[(v << (3-b)) + hi],
@@ -74,18 +85,21 @@ __device__ __forceinline__ ulonglong2 ldg_tw(const ulonglong2* p) {
 //        warp-tiled copy  t0[t / 32][j][t % 32],  j = (2^(3-b) - 1) + hi in [0,15),  t = (residue index) / 16,
 //        so the lanes of a warp read consecutive 16-byte entries and the 15 loads of a thread are ONE pointer
 //        plus immediate offsets j * 512 bytes (no per-load address arithmetic, nothing to hoist and spill).
+template <class E>
 struct TwStd {
-    const ulonglong2* __restrict__ tw; u32 v;
+    const E* __restrict__ tw; u32 v;
     __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(tw + ((v << (3 - b)) + hi)); }
 };
 //  Sm   : the same indexing as Std, out of a copy of the table's first entries staged in shared memory (the
 //        column kernels: all tiles of a limb use entries [1, 2^T) only, 4 KB).
+template <class E>
 struct TwSm {
-    const ulonglong2* s; u32 v;
-    __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return s[(v << (3 - b)) + hi]; }
+    const E* s; u32 v;
+    __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return tw_expand(s[(v << (3 - b)) + hi]); }
 };
+template <class E>
 struct TwT0 {
-    const ulonglong2* __restrict__ p;                  // t0 + (t / 32) * kT0Block + t % 32
+    const E* __restrict__ p;                  // t0 + (t / 32) * kT0Block + t % 32
     __device__ __forceinline__ ulonglong2 get(int b, int hi) const { return ldg_tw(p + ((((1 << (3 - b)) - 1) + hi) << 5)); }
 };
 
@@ -302,19 +316,20 @@ struct Sched {
 };
 
 // Per-limb twiddle tables (already offset to the limb) and the ring degree.
+template <class E>   // E = entry type: ulonglong2 {w, shoup(w)} / {w, w/q}, or u64 for the compact form of the 32-bit policies
 struct TwTab {
-    const ulonglong2* __restrict__ tw;   // [N]       standard bit-reversed table
-    const ulonglong2* __restrict__ t0;   // [N/512][15][32] warp-tiled copy for the window at bit 0
+    const E* __restrict__ tw;   // [N]       standard bit-reversed table
+    const E* __restrict__ t0;   // [N/512][15][32] warp-tiled copy for the window at bit 0
     u32 N;
 };
 // Twiddle source of the round whose window sits at slab bit P0; off = offset of the slab in its polynomial.
-template <int P0>
-__device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
+template <int P0, class E>
+__device__ __forceinline__ auto round_tw(const TwTab<E>& T, u32 off, u32 tid) {
     if constexpr (P0 == 0) {
         const u32 t = (off >> 4) + tid;
-        return TwT0{T.t0 + ((t >> 5) * kT0Block + (t & 31u))};
+        return TwT0<E>{T.t0 + ((t >> 5) * kT0Block + (t & 31u))};
     }
-    else return TwStd{T.tw, ((T.N + off) >> (P0 + 4)) + (tid >> P0)};
+    else return TwStd<E>{T.tw, ((T.N + off) >> (P0 + 4)) + (tid >> P0)};
 }
 
 // ---- forward transform of a slab: the LOGS low stages --------------------------------------------
@@ -322,7 +337,7 @@ __device__ __forceinline__ auto round_tw(const TwTab& T, u32 off, u32 tid) {
 // (window at bit 0: 16 contiguous residues per thread).  The slab may be a tile of several independent
 // 2^LOGS-point sub-transforms (tid then spans more than 2^(LOGS-4) threads): nothing here depends on it.
 template <class A, int LOGS, int ENTRY = 16>
-__device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
+__device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab<typename A::tw_t>& T, u32 off,
                                          typename A::word C, typename A::word nq) {
     using S = Sched<LOGS>;
     // stages done before round k: LOGS - top(k); ENTRY is the range bound of the slab's inputs (fwd_bound)
@@ -351,7 +366,7 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
 // Entry layout: window at bit 0; exit layout: window at bit p0(0).
 // LAST: the slab is the whole polynomial (N == 2^LOGS), so the top stage folds N^-1.
 template <class A, int LOGS, bool LAST, bool FRESH = false>
-__device__ __forceinline__ void slab_inv(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab& T, u32 off,
+__device__ __forceinline__ void slab_inv(typename A::word (&r)[kElems], typename A::word* sm, u32 tid, const TwTab<typename A::tw_t>& T, u32 off,
                                          typename A::word C, typename A::word nq, const LimbParams* __restrict__ Pg) {
     using S = Sched<LOGS>;
     if constexpr (S::NR > 2) {

@@ -98,9 +98,11 @@ __device__ __forceinline__ TileId tile_id(u32 logN, u32 B, u32 limb0) {
     s.limb = limb0 + p / B;
     return s;
 }
-__device__ __forceinline__ TwTab limb_tables(const Tables& T, u32 limb, u32 logN) {
+template <class A>
+__device__ __forceinline__ TwTab<typename A::tw_t> limb_tables(const Tables& T, u32 limb, u32 logN) {
+    typedef typename A::tw_t E;
     const size_t N = (size_t)1 << logN;
-    return TwTab{T.tw + limb * N, T.t0 + limb * t0_entries(N), (u32)N};
+    return TwTab<E>{reinterpret_cast<const E*>(T.tw) + limb * N, reinterpret_cast<const E*>(T.t0) + limb * t0_entries(N), (u32)N};
 }
 
 // Per-limb scalars every kernel needs: Cf/Ci = offset constants of the arithmetic policy.
@@ -236,7 +238,7 @@ k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    const TwTab T = limb_tables(tabs, s.limb, logN);
+    const auto T = limb_tables<A>(tabs, s.limb, logN);
     prefetch_row_tile<LOGT, RowPf<A>::kFwd>(in, tid);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
@@ -278,7 +280,7 @@ k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs
     const TileId s = tile_id<LOGT>(logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    const TwTab T = limb_tables(tabs, s.limb, logN);
+    const auto T = limb_tables<A>(tabs, s.limb, logN);
     prefetch_row_tile<LOGT, RowPf<A>::kInv>(in, tid);
     W r[kElems];
     if constexpr (LOGT > 4) {
@@ -357,8 +359,8 @@ k_row_polymul(const typename A::store* a, const typename A::store* b, typename A
     prefetch_row_tile<LOGT, GFHE_PF_MUL>(b, tid);
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    const TwTab Tf = limb_tables(tf, s.limb, logN);
-    const TwTab Ti = limb_tables(ti, s.limb, logN);
+    const auto Tf = limb_tables<A>(tf, s.limb, logN);
+    const auto Ti = limb_tables<A>(ti, s.limb, logN);
     constexpr int P0 = Sched<LOGS>::p0(0);
     W r[kElems];
 #pragma unroll
@@ -503,7 +505,7 @@ k_row_polymul_persist(const typename A::store* a, const typename A::store* b, ty
         s.limb = limb0 + (u32)(s.g0 >> logN) / B;
         const LimbParams* __restrict__ Pg = tf.params + s.limb;
         const LimbK<W> K = limb_consts<A>(Pg);
-        const TwTab Tf = limb_tables(tf, s.limb, logN);
+        const auto Tf = limb_tables<A>(tf, s.limb, logN);
         W r[kElems];
         mbar_wait(barA, par);
 #pragma unroll
@@ -519,7 +521,7 @@ k_row_polymul_persist(const typename A::store* a, const typename A::store* b, ty
         // for twiddles, from a's transform into b's) they spill ~40 registers under the 128-register cap
         u32 limb_b = s.limb;
         asm volatile("" : "+r"(limb_b));
-        slab_fwd<A, LOGS>(r, sm0, tid, limb_tables(tf, limb_b, logN), s.off, K.Cf, K.nq);   // ... and every read of smb before the refill below
+        slab_fwd<A, LOGS>(r, sm0, tid, limb_tables<A>(tf, limb_b, logN), s.off, K.Cf, K.nq);   // ... and every read of smb before the refill below
         if (tid == 0 && next < ntiles) tma_tile_issue(smb, b + ((u64)next << LOGT), kTileBytes, barB);
         fwd_semi_all<A>(r, K, Pg);
         if constexpr (A::kFloat) {
@@ -558,7 +560,7 @@ k_row_polymul_persist(const typename A::store* a, const typename A::store* b, ty
         asm volatile("" : "+r"(limb_i));
         const LimbParams* __restrict__ Pi = tf.params + limb_i;
         const LimbK<W> Ki = limb_consts<A>(Pi);
-        slab_inv<A, LOGS, false>(r, sm0, tid, limb_tables(ti, limb_i, logN), s.off, Ki.Ci, Ki.nq, Pi);
+        slab_inv<A, LOGS, false>(r, sm0, tid, limb_tables<A>(ti, limb_i, logN), s.off, Ki.Ci, Ki.nq, Pi);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = A::to_raw(r[i]);
         __syncthreads();   // sm0 is reused by the next trip's forward exchange
@@ -610,21 +612,22 @@ k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename 
     St* out = (blockIdx.y ? out1 : out0) + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    __shared__ ulonglong2 tws[256];
+    typedef typename A::tw_t E;
+    __shared__ E tws[256];
     W r[kElems];
     {
         const St* p = in + Geo::template toff<8>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
-    tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
+    tws[tid] = __ldg(reinterpret_cast<const E*>(tabs.tw) + ((size_t)id.limb << Geo::LOGN) + tid);   // the column pass reads entries [1, 2^T) only
     GFHE_SYNC();
-    fwd_round<A, 3, Geo::LO8, TwSm, 1>(r, TwSm{tws, 1u}, K.Cf, K.nq);   // canonical inputs: the range schedule starts from q
+    fwd_round<A, 3, Geo::LO8, TwSm<E>, 1>(r, TwSm<E>{tws, 1u}, K.Cf, K.nq);   // canonical inputs: the range schedule starts from q
     if constexpr (Geo::TWO) {
         sm_store<8>(sm, tid, r);
         GFHE_SYNC();
         sm_load<4>(sm, tid, r);
-        fwd_round<A, 3, Geo::LO4, TwSm, fwd_bound(1, 4 - Geo::LO8)>(r, TwSm{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
+        fwd_round<A, 3, Geo::LO4, TwSm<E>, fwd_bound(1, 4 - Geo::LO8)>(r, TwSm<E>{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         St* p = out + Geo::template toff<4>(tid);
 #pragma unroll
         for (int i = 0; i < kElems; ++i) p[Geo::template roff<4>(i)] = A::to_raw(r[i]);
@@ -648,7 +651,8 @@ k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables ta
     St* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    __shared__ ulonglong2 tws[256];
+    typedef typename A::tw_t E;
+    __shared__ E tws[256];
     W r[kElems];
     if constexpr (Geo::TWO) {
         const St* p = in + Geo::template toff<4>(tid);
@@ -659,15 +663,15 @@ k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables ta
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<8>(i)], tid * 77u + i);
     }
-    tws[tid] = __ldg(tabs.tw + ((size_t)id.limb << Geo::LOGN) + tid);
+    tws[tid] = __ldg(reinterpret_cast<const E*>(tabs.tw) + ((size_t)id.limb << Geo::LOGN) + tid);
     GFHE_SYNC();
     if constexpr (Geo::TWO) {
-        inv_round<A, 3, Geo::LO4, false>(r, TwSm{tws, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
+        inv_round<A, 3, Geo::LO4, false>(r, TwSm<E>{tws, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
         sm_store<4>(sm, tid, r);
         GFHE_SYNC();
         sm_load<8>(sm, tid, r);
     }
-    inv_round<A, 3, Geo::LO8, true>(r, TwSm{tws, 1u}, K.Ci, K.nq, Pg);
+    inv_round<A, 3, Geo::LO8, true>(r, TwSm<E>{tws, 1u}, K.Ci, K.nq, Pg);
     St* p = out + Geo::template toff<8>(tid);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_u64(r[i]);

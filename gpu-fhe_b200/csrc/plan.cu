@@ -149,14 +149,23 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
                 }
             });
         for (auto& th : pool) th.join();
-        e = cudaMalloc(&pl->d_fwd, bytes);
-        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv, bytes);
-        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd, hf, bytes, cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv, hi, bytes, cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMalloc(&pl->d_fwd_t0, bytes0);
-        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv_t0, bytes0);
-        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd_t0, hf0, bytes0, cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv_t0, hi0, bytes0, cudaMemcpyHostToDevice);
+        size_t up = bytes, up0 = bytes0;
+        if (pl->w32) {   // 32-bit policy: compact 8-byte entries w | (w' << 32), w' = high word of the Shoup constant (ntt_core.cuh, tw_expand)
+            for (ulonglong2* tab : {hf, hi, hf0, hi0}) {
+                const size_t n = (tab == hf || tab == hi) ? N * L : n0 * L;
+                u64* dst = reinterpret_cast<u64*>(tab);   // in place: entry i is written at byte 8i, read at byte 16i
+                for (size_t i = 0; i < n; ++i) { const ulonglong2 v = tab[i]; dst[i] = (v.x & 0xffffffffull) | (v.y & 0xffffffff00000000ull); }
+            }
+            up = bytes / 2; up0 = bytes0 / 2;
+        }
+        e = cudaMalloc(&pl->d_fwd, up);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv, up);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd, hf, up, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv, hi, up, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_fwd_t0, up0);
+        if (e == cudaSuccess) e = cudaMalloc(&pl->d_inv_t0, up0);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_fwd_t0, hf0, up0, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(pl->d_inv_t0, hi0, up0, cudaMemcpyHostToDevice);
         std::free(hf); std::free(hi); std::free(hf0); std::free(hi0);
         if (e != cudaSuccess) { plan_destroy(pl); return (int)e; }
     }

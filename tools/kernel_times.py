@@ -10,12 +10,15 @@ N, L, B, bits = 65536, 32, 16, int(os.environ.get("BITS", "60"))
 moduli = P.ntt_primes(bits, L); plan = P.make_plan(N, moduli, device=0); lib = _capi.lib
 rng = np.random.default_rng(0)
 h = np.stack([rng.integers(0, q, (B, N), dtype=np.uint64) for q in moduli]).view(np.int64)
+PACKED = os.environ.get("PACKED") == "1"      # packed 32-bit layout (BITS=30 only)
+if PACKED: h = h.astype(np.int32)
 a = torch.from_numpy(h).cuda(); b = torch.from_numpy(h[::-1].copy()).cuda(); c = torch.empty_like(a)
+f_mul, f_fwd, f_inv = (lib.gfhe_poly_mul_u32, lib.gfhe_ntt_forward_u32, lib.gfhe_ntt_inverse_u32) if PACKED else (lib.gfhe_poly_mul, lib.gfhe_ntt_forward, lib.gfhe_ntt_inverse)
 wsb = lib.gfhe_poly_mul_workspace_bytes(plan.handle, L, B); ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-def pm(): lib.gfhe_poly_mul(plan.handle, 0, L, B, a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), wsb, st)
-def nt(): lib.gfhe_ntt_forward(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
-def it(): lib.gfhe_ntt_inverse(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
+def pm(): f_mul(plan.handle, 0, L, B, a.data_ptr(), b.data_ptr(), c.data_ptr(), ws.data_ptr(), wsb, st)
+def nt(): f_fwd(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
+def it(): f_inv(plan.handle, 0, L, B, a.data_ptr(), c.data_ptr(), st)
 for name, f in (("polymul", pm), ("ntt", nt), ("intt", it)):
     for _ in range(5): f()
     torch.cuda.synchronize()

@@ -36,6 +36,11 @@ SYMBOLS = {
     "gfhe_ntt_inverse_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_poly_mul_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp, ctypes.c_size_t, vp]),
     "gfhe_poly_mul_pre_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
+    "gfhe_vec_add_i32": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_vec_sub_i32": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_vec_mul_i32": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_ntt_mul_acc_u32": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, u32, vp, vp, ctypes.c_uint64, vp, vp]),
+    "gfhe_automorphism_u32": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_mul_acc": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, u32, vp, vp, ctypes.c_uint64, vp, vp]),
     "gfhe_automorphism": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),

@@ -197,6 +197,40 @@ int gfhe_poly_mul_pre_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_
     return (int)launch_poly_mul_pre_u32(*P(plan), limb0, nl, d_a, d_b_ntt, d_c, batch, S(stream));
 }
 
+static int vec_op_i32(int op, gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner,
+                      const int32_t* a, const int32_t* b, int32_t* out, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (!P(plan)->w32) return GFHE_ELAYOUT;
+    if (inner == 0) return 0;
+    if (!a || !b || !out) return GFHE_EARG;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_vec_op_u32(op, *P(plan), limb0, nl, a, b, out, inner, S(stream));
+}
+int gfhe_vec_add_i32(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int32_t* a, const int32_t* b, int32_t* o, void* s) { return vec_op_i32(0, p, l0, nl, inner, a, b, o, s); }
+int gfhe_vec_sub_i32(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int32_t* a, const int32_t* b, int32_t* o, void* s) { return vec_op_i32(1, p, l0, nl, inner, a, b, o, s); }
+int gfhe_vec_mul_i32(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int32_t* a, const int32_t* b, int32_t* o, void* s) { return vec_op_i32(2, p, l0, nl, inner, a, b, o, s); }
+
+int gfhe_ntt_mul_acc_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner, uint32_t terms,
+                         const uint32_t* d_a, const uint32_t* d_b, uint64_t term_stride, uint32_t* d_out, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (!P(plan)->w32) return GFHE_ELAYOUT;
+    if (inner == 0) return 0;
+    if (!d_a || !d_b || !d_out || terms == 0) return GFHE_EARG;
+    if (terms > 1 && (d_out == d_a || d_out == d_b)) return GFHE_EARG;
+    if (terms > 65536u) return GFHE_ETERMS;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_mul_acc_u32(*P(plan), limb0, nl, inner, terms, d_a, d_b, term_stride, d_out, S(stream));
+}
+
+int gfhe_automorphism_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch, uint32_t k, int ntt_domain,
+                          const uint32_t* d_in, uint32_t* d_out, void* stream) {
+    if (int rc = check_packed(P(plan), limb0, nl)) return rc;
+    if (!d_in || !d_out || batch == 0 || d_in == d_out) return GFHE_EARG;
+    if ((k & 1u) == 0) return GFHE_EGALOIS;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_automorphism_u32(*P(plan), limb0, nl, batch, k, ntt_domain != 0, d_in, d_out, S(stream));
+}
+
 int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_t inner, uint32_t terms,
                      const uint64_t* d_a, const uint64_t* d_b, uint64_t term_stride, uint64_t* d_out, void* stream) {
     if (int rc = check_range(P(plan), limb0, nl)) return rc;

@@ -82,6 +82,14 @@ cudaError_t launch_poly_mul_pre_u32(const Plan& pl, u32 limb0, u32 nl, const u32
 cudaError_t launch_vec_op(int op, const Plan& pl, u32 limb0, u32 nl, const long long* a, const long long* b,
                           long long* out, u64 inner, cudaStream_t st);
 
+// packed_kernels.cu -- the operations around the transforms on the packed 32-bit layout (plans with every modulus below 2^30)
+cudaError_t launch_vec_op_u32(int op, const Plan& pl, u32 limb0, u32 nl, const int* a, const int* b, int* out, u64 inner,
+                              cudaStream_t st);
+cudaError_t launch_mul_acc_u32(const Plan& pl, u32 limb0, u32 nl, u64 inner, u32 terms, const u32* a, const u32* b,
+                               u64 term_stride, u32* out, cudaStream_t st);
+cudaError_t launch_automorphism_u32(const Plan& pl, u32 limb0, u32 nl, u32 B, u32 k, bool ntt_domain, const u32* in, u32* out,
+                                    cudaStream_t st);
+
 // ring_kernels.cu -- NTT-domain multiply-accumulate and the Galois automorphism X -> X^k
 cudaError_t launch_mul_acc(const Plan& pl, u32 limb0, u32 nl, u64 inner, u32 terms, const u64* a, const u64* b,
                            u64 term_stride, u64* out, cudaStream_t st);

@@ -111,7 +111,7 @@ def _vec_moduli(MOD, shape: Tuple[int, ...]) -> Tuple[Tuple[int, ...], int]:
 def vec_op(op: int, a, b, MOD):
     A = _Arg(a)
     B = _Arg(b, A.t.device)
-    _no_packed(A, B)
+    _same_layout(A, B)
     if B.t.device != A.t.device:
         raise ValueError("operands live on different devices")
     moduli, inner = _vec_moduli(MOD, A.shape)
@@ -120,8 +120,8 @@ def vec_op(op: int, a, b, MOD):
         return A.wrap(out)
     dev = A.t.device
     plan = ring.get_plan(dev.index, 0, moduli)
-    fn = getattr(_capi.lib, _VEC_FN[op])
-    _capi.check(fn(plan.handle, 0, len(moduli), inner, _ptr(A.t), _ptr(B.t), _ptr(out), _stream(dev)), _VEC_FN[op])
+    name = _VEC_FN[op] + ("_i32" if A.packed else "")
+    _capi.check(getattr(_capi.lib, name)(plan.handle, 0, len(moduli), inner, _ptr(A.t), _ptr(B.t), _ptr(out), _stream(dev)), name)
     return A.wrap(out)
 
 
@@ -130,12 +130,6 @@ def vec_op(op: int, a, b, MOD):
 def _same_layout(a: "_Arg", b: "_Arg") -> None:
     if a.packed != b.packed:
         raise TypeError("operands must use the same word size (both 64-bit or both packed 32-bit)")
-
-
-def _no_packed(*args: "_Arg") -> None:
-    for a in args:
-        if a.packed:
-            raise TypeError("this operation has no packed 32-bit form yet: pass int64/uint64 residues")
 
 
 def _lbn(shape: Sequence[int], L: int) -> Tuple[int, int, int]:
@@ -223,7 +217,7 @@ def mul_acc(a, b, MOD, stacked: bool):
         b = torch.stack([_Arg(x).t for x in b]) if not isinstance(b[0], np.ndarray) else np.stack(b)
     A = _Arg(a)
     Bv = _Arg(b, A.t.device)
-    _no_packed(A, Bv)
+    _same_layout(A, Bv)
     if A.shape != Bv.shape:
         raise AssertionError("operands must have equal shapes")
     L = len(moduli)
@@ -241,8 +235,8 @@ def mul_acc(a, b, MOD, stacked: bool):
     out = torch.empty(item, dtype=A.t.dtype, device=dev)
     if inner == 0:
         return A.wrap(out)
-    _capi.check(_capi.lib.gfhe_ntt_mul_acc(plan.handle, 0, Lq, inner, K, _ptr(A.t), _ptr(Bv.t), Lq * inner, _ptr(out),
-                                           _stream(dev)), "gfhe_ntt_mul_acc")
+    fn = _capi.lib.gfhe_ntt_mul_acc_u32 if A.packed else _capi.lib.gfhe_ntt_mul_acc
+    _capi.check(fn(plan.handle, 0, Lq, inner, K, _ptr(A.t), _ptr(Bv.t), Lq * inner, _ptr(out), _stream(dev)), "gfhe_ntt_mul_acc")
     return A.wrap(out)
 
 
@@ -250,7 +244,6 @@ def automorphism(x, k: int, MOD, ntt_domain: bool):
     """a(X) -> a(X^k), k odd, on every limb-polynomial of x ([L, B, N]); out of place."""
     moduli = ring.resolve_moduli(MOD)
     X = _Arg(x)
-    _no_packed(X)
     L, B, N = _lbn(X.shape, len(moduli))
     k = int(k) % (2 * N)
     if k % 2 == 0:
@@ -260,8 +253,8 @@ def automorphism(x, k: int, MOD, ntt_domain: bool):
     out = torch.empty_like(X.t)
     if B == 0:
         return X.wrap(out)
-    _capi.check(_capi.lib.gfhe_automorphism(plan.handle, 0, L, B, k, int(bool(ntt_domain)), _ptr(X.t), _ptr(out),
-                                            _stream(dev)), "gfhe_automorphism")
+    fn = _capi.lib.gfhe_automorphism_u32 if X.packed else _capi.lib.gfhe_automorphism
+    _capi.check(fn(plan.handle, 0, L, B, k, int(bool(ntt_domain)), _ptr(X.t), _ptr(out), _stream(dev)), "gfhe_automorphism")
     return X.wrap(out)
 
 

@@ -101,6 +101,20 @@ int gfhe_poly_mul_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint
 int gfhe_poly_mul_pre_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
                           const uint32_t* d_a, const uint32_t* d_b_ntt, uint32_t* d_c, void* stream);
 
+/* ... and the operations around them on the same layout: element-wise ops on ANY int32 inputs (Python % semantics,
+ * canonical outputs), the NTT-domain multiply-accumulate (up to 65536 terms) and the automorphism.  Same contracts as
+ * gfhe_vec_add/_sub/_mul, gfhe_ntt_mul_acc and gfhe_automorphism below. */
+int gfhe_vec_add_i32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const int32_t* d_a, const int32_t* d_b, int32_t* d_out, void* stream);
+int gfhe_vec_sub_i32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const int32_t* d_a, const int32_t* d_b, int32_t* d_out, void* stream);
+int gfhe_vec_mul_i32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const int32_t* d_a, const int32_t* d_b, int32_t* d_out, void* stream);
+int gfhe_ntt_mul_acc_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner, uint32_t terms,
+                         const uint32_t* d_a, const uint32_t* d_b, uint64_t term_stride, uint32_t* d_out, void* stream);
+int gfhe_automorphism_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch, uint32_t k, int ntt_domain,
+                          const uint32_t* d_in, uint32_t* d_out, void* stream);
+
 /* out = (a op b) mod q_l, exact for ANY int64 inputs (Python % semantics, result in [0, q)).
  * Buffers are [num_limbs, inner]; limb l of the range uses modulus limb0 + l. */
 int gfhe_vec_add(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,

@@ -629,10 +629,49 @@ def test_packed_u32_layout_errors(cuda_device):
     with P.ring(m30):
         with pytest.raises(TypeError):
             P.poly_mul(x, x.to(torch.int64))                         # mixed word sizes
-        with pytest.raises(TypeError):
-            P.automorphism(x, 5)                                     # no packed form yet
-    with pytest.raises(TypeError):
-        P.vec_add(x, x, np.array(m30, dtype=np.int64).reshape(2, 1, 1))
+    with pytest.raises(_capi.GpuFheError) as e:
+        P.vec_add(x, x, np.array(P.ntt_primes(50, 2), dtype=np.int64).reshape(2, 1, 1))
+    assert e.value.code == -12
+
+
+def test_packed_u32_elementwise_mac_automorphism(cuda_device):
+    """The operations around the transforms on int32 tensors: same residues as the int64 kernels (which are pinned to
+    the reference's outputs and the oracle), for ANY int32 inputs of the element-wise ops."""
+    import polynomial as P
+    N, L, B = 1 << 10, 3, 5
+    moduli = P.ntt_primes(30, L, N=1 << 12)
+    MOD = np.array(moduli, dtype=np.int64).reshape(L, 1, 1)
+    rng = np.random.default_rng(77)
+    a = rng.integers(-2**31, 2**31, (L, B, N), dtype=np.int64)
+    b = rng.integers(-2**31, 2**31, (L, B, N), dtype=np.int64)
+    a[:, 0, :4] = [-2**31, 2**31 - 1, 0, -1]
+    b[:, 0, :4] = [-2**31, 2**31 - 1, -1, 2**31 - 1]
+    ta, tb = torch.from_numpy(a).to(cuda_device), torch.from_numpy(b).to(cuda_device)
+    pa, pb = ta.to(torch.int32), tb.to(torch.int32)
+    ao, bo, mo = a.astype(object), b.astype(object), MOD.astype(object)
+    for op, want in ((P.vec_add, (ao + bo) % mo), (P.vec_sub, (ao - bo) % mo), (P.vec_mul, (ao * bo) % mo)):   # arithmetic.py:5,9,13 on Python ints
+        got = op(pa, pb, MOD)
+        assert got.dtype == torch.int32
+        assert torch.equal(got.to(torch.int64), op(ta, tb, MOD))
+        assert np.array_equal(got.cpu().numpy().astype(object), want)
+    odd = op(pa[:, :, :1001].contiguous(), pb[:, :, :1001].contiguous(), MOD)
+    assert torch.equal(odd.to(torch.int64), P.vec_mul(ta[:, :, :1001].contiguous(), tb[:, :, :1001].contiguous(), MOD))
+    # canonical residues for the NTT-domain ops
+    ra, rb = rand_lbn(71, moduli, B, N), rand_lbn(72, moduli, B, N)
+    ua, ub = dev_i64(ra, cuda_device), dev_i64(rb, cuda_device)
+    with P.ring(moduli):
+        for K in (1, 3, 8, 19):
+            sa = torch.stack([(ua + 7 * t) % torch.from_numpy(MOD).to(cuda_device) for t in range(K)])
+            sb = torch.stack([(ub + 11 * t) % torch.from_numpy(MOD).to(cuda_device) for t in range(K)])
+            want = P.poly_mac_ntt(list(sa), list(sb))
+            got = P.poly_mac_ntt(list(sa.to(torch.int32)), list(sb.to(torch.int32)))
+            assert got.dtype == torch.int32 and torch.equal(got.to(torch.int64), want)
+        for k in (3, 5, 2 * N - 1, 1025):
+            for ntt in (False, True):
+                got = P.automorphism(ua.to(torch.int32), k, ntt=ntt)
+                assert torch.equal(got.to(torch.int64), P.automorphism(ua, k, ntt=ntt))
+
+
 
 
 def test_empty_and_non_contiguous_operands(cuda_device):

@@ -45,12 +45,13 @@ struct TileGeo {
 };
 
 // resident CTAs per SM the stand-alone row passes are compiled for.  32-bit words need half the registers; four resident
-// CTAs pay on the packed layout (2^16 NTT 0.200 -> 0.177 ms) and not on the 64-bit one, which is DRAM-bound (0.226 -> 0.229)
+// CTAs pay on the packed layout (2^16 NTT 0.200 -> 0.177 ms) and, once the twiddle entries are compact, on the 64-bit
+// layout too (k_row_fwd 0.099 -> 0.095 ms, k_row_inv 0.095 -> 0.091 ms)
 #ifndef GFHE_ROWB32
 #define GFHE_ROWB32 4
 #endif
 template <class A, int LOGT>
-struct RowOcc { static constexpr int kB = LOGT == 12 ? (sizeof(typename A::store) == 4 ? GFHE_ROWB32 : GFHE_ROWB) : 1; };
+struct RowOcc { static constexpr int kB = LOGT == 12 ? (sizeof(typename A::word) == 4 ? GFHE_ROWB32 : GFHE_ROWB) : 1; };
 
 struct Tables {   // kernel argument: the plan's device tables
     const ulonglong2* tw;    // [L][N]

@@ -322,31 +322,37 @@ def run_b200(args, rank, world, local_rank):
     del da4, db4
 
     # ---- the same shape with 30-bit moduli ("32-bit where the moduli fit"): 64-bit layout and packed int32 layout
-    m30 = P.ntt_primes(30, L_TOTAL)[sh.limbs[0]:sh.limbs[1]]
-    plan30 = P.make_plan(N, m30, device=local_rank)
-    red = torch.tensor(m30, dtype=torch.int64, device=dev).view(nl, 1, 1)
-    a30, b30 = da % red, db % red
-    c30 = torch.empty_like(a30)
-    a30p, b30p = a30.to(torch.int32), b30.to(torch.int32)
-    c30p = torch.empty_like(a30p)
+    narrow, narrow_err = {}, None
+    try:   # an auxiliary section: a failure here is reported, it does not void the headline
+        m30 = P.ntt_primes(30, L_TOTAL)[sh.limbs[0]:sh.limbs[1]]
+        plan30 = P.make_plan(N, m30, device=local_rank)
+        red = torch.tensor(m30, dtype=torch.int64, device=dev).view(nl, 1, 1)
+        a30, b30 = da % red, db % red
+        c30 = torch.empty_like(a30)
+        a30p, b30p = a30.to(torch.int32), b30.to(torch.int32)
+        c30p = torch.empty_like(a30p)
 
-    def call30(fn, *ptrs):
-        def f():
-            rc = fn(plan30.handle, 0, nl, nb, *ptrs)
-            if rc:
-                raise RuntimeError(_capi.error_string(rc))
-        return f
-    narrow = {}
-    for name, fn, ptrs, word in (
-            ("poly_mul", lib.gfhe_poly_mul, (a30.data_ptr(), b30.data_ptr(), c30.data_ptr(), ws.data_ptr(), ws_bytes, st), 8),
-            ("ntt", lib.gfhe_ntt_forward, (a30.data_ptr(), c30.data_ptr(), st), 8),
-            ("intt", lib.gfhe_ntt_inverse, (a30.data_ptr(), c30.data_ptr(), st), 8),
-            ("poly_mul_packed", lib.gfhe_poly_mul_u32, (a30p.data_ptr(), b30p.data_ptr(), c30p.data_ptr(), ws.data_ptr(), ws_bytes, st), 4),
-            ("ntt_packed", lib.gfhe_ntt_forward_u32, (a30p.data_ptr(), c30p.data_ptr(), st), 4),
-            ("intt_packed", lib.gfhe_ntt_inverse_u32, (a30p.data_ptr(), c30p.data_ptr(), st), 4)):
-        narrow[name] = (timed(call30(fn, *ptrs), Ks, W) / Ks, word)
-    assert torch.equal(c30p.to(torch.int64), c30), "packed and 64-bit layouts disagree"     # both hold iNTT(a30)
-    del a30, b30, c30, a30p, b30p, c30p
+        def call30(fn, *ptrs):
+            def f():
+                rc = fn(plan30.handle, 0, nl, nb, *ptrs)
+                if rc:
+                    raise RuntimeError(_capi.error_string(rc))
+            return f
+        for name, fn, ptrs, word in (
+                ("poly_mul", lib.gfhe_poly_mul, (a30.data_ptr(), b30.data_ptr(), c30.data_ptr(), ws.data_ptr(), ws_bytes, st), 8),
+                ("ntt", lib.gfhe_ntt_forward, (a30.data_ptr(), c30.data_ptr(), st), 8),
+                ("intt", lib.gfhe_ntt_inverse, (a30.data_ptr(), c30.data_ptr(), st), 8),
+                ("poly_mul_packed", lib.gfhe_poly_mul_u32, (a30p.data_ptr(), b30p.data_ptr(), c30p.data_ptr(), ws.data_ptr(), ws_bytes, st), 4),
+                ("ntt_packed", lib.gfhe_ntt_forward_u32, (a30p.data_ptr(), c30p.data_ptr(), st), 4),
+                ("intt_packed", lib.gfhe_ntt_inverse_u32, (a30p.data_ptr(), c30p.data_ptr(), st), 4)):
+            narrow[name] = (timed(call30(fn, *ptrs), Ks, W) / Ks, word)
+        assert torch.equal(c30p.to(torch.int64), c30), "packed and 64-bit layouts disagree"     # both hold iNTT(a30)
+        del a30, b30, c30, a30p, b30p, c30p
+    except Exception as exc:   # noqa: BLE001
+        if world > 1:
+            raise          # the timed sections hold barriers: a rank that skipped them would hang the others
+        narrow_err = "%s: %s" % (type(exc).__name__, exc)
+        log("moduli_30bit section failed:", narrow_err)
     clocks.active = False
 
     # ---- e2e: host buffers through the C-ABI host entry point (pinned memory, copies inside)
@@ -446,7 +452,7 @@ def run_b200(args, rank, world, local_rank):
                    "bytes_per_residue": (3 if name.startswith("poly_mul") else 2) * word,
                    "achieved_GBs": (3 if name.startswith("poly_mul") else 2) * word * N * UNITS_PER_GPU / (ms * 1e-3) / 1e9,
                    "frac": (3 if name.startswith("poly_mul") else 2) * word * N * UNITS_PER_GPU / (ms * 1e-3) / 1e9 / peak}
-            for name, (ms, word) in narrow.items()},
+            for name, (ms, word) in narrow.items()} if narrow_err is None else {"error": narrow_err},
         "ntt": {"metric": "limb_ntt_per_s", "value": ntt_value, "unit": "limb-NTT/s", "ms_per_step": ms_ntt / K,
                 "achieved_GBs": ntt_gbs, "frac": ntt_gbs / peak, "frac_of_8TBs_nominal": ntt_gbs / 8000.0,
                 "inverse": {"value": units * K / (ms_intt * 1e-3), "ms_per_step": ms_intt / K,

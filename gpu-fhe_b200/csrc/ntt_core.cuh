@@ -278,9 +278,12 @@ __device__ __forceinline__ void inv_round(typename A::word (&r)[kElems], const T
 
 // ---- shared-memory re-distribution ---------------------------------------------------------------
 template <class W> struct __align__(16) W2 { W x, y; };   // 16-byte pair of 8-byte words (u64 or double)
-template <int P0, class W>
+// PK = padding words per 16-word row.  2 keeps 8-byte words (and the 8-byte-aligned pairs of 32-bit words the row kernels
+// move) conflict-free; the column kernels' scalar exchange of 32-bit words wants 1 (two half-warps 272 = 16 mod 32 words apart).
+template <int PK> __host__ __device__ constexpr u32 padk(u32 e) { return e + ((e >> 4) * PK); }
+template <int P0, class W, int PK = 2>
 __device__ __forceinline__ void sm_store(W* sm, u32 tid, const W (&r)[kElems]) {
-    W* p = sm + pad(elem_index<P0>(tid, 0));
+    W* p = sm + padk<PK>(elem_index<P0>(tid, 0));
     if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -289,12 +292,12 @@ __device__ __forceinline__ void sm_store(W* sm, u32 tid, const W (&r)[kElems]) {
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) p[pad((u32)i << P0)] = r[i];
+        for (int i = 0; i < kElems; ++i) p[padk<PK>((u32)i << P0)] = r[i];
     }
 }
-template <int P0, class W>
+template <int P0, class W, int PK = 2>
 __device__ __forceinline__ void sm_load(const W* sm, u32 tid, W (&r)[kElems]) {
-    const W* p = sm + pad(elem_index<P0>(tid, 0));
+    const W* p = sm + padk<PK>(elem_index<P0>(tid, 0));
     if constexpr (P0 == 0 && sizeof(W) == 8) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -303,7 +306,7 @@ __device__ __forceinline__ void sm_load(const W* sm, u32 tid, W (&r)[kElems]) {
         }
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = p[pad((u32)i << P0)];
+        for (int i = 0; i < kElems; ++i) r[i] = p[padk<PK>((u32)i << P0)];
     }
 }
 

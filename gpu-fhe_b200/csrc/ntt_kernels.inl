@@ -589,6 +589,7 @@ struct ColGeo {
     template <int P0> __host__ __device__ static constexpr u32 roff(int i) { return off_c((u32)i << P0); }
 };
 struct ColId { u64 base; u32 limb; };
+template <class W> constexpr int kColPad = sizeof(W) == 4 ? 1 : 2;   // padding of the column kernels' exchange (ntt_core.cuh, padk)
 template <int LOGC, int S>
 __device__ __forceinline__ ColId col_id(u32 B, u32 limb0) {
     using Geo = ColGeo<LOGC, S>;
@@ -625,9 +626,9 @@ k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename 
     GFHE_SYNC();
     fwd_round<A, 3, Geo::LO8, TwSm<E>, 1>(r, TwSm<E>{tws, 1u}, K.Cf, K.nq);   // canonical inputs: the range schedule starts from q
     if constexpr (Geo::TWO) {
-        sm_store<8>(sm, tid, r);
+        sm_store<8, W, kColPad<W>>(sm, tid, r);
         GFHE_SYNC();
-        sm_load<4>(sm, tid, r);
+        sm_load<4, W, kColPad<W>>(sm, tid, r);
         fwd_round<A, 3, Geo::LO4, TwSm<E>, fwd_bound(1, 4 - Geo::LO8)>(r, TwSm<E>{tws, 16u + (tid >> 4)}, K.Cf, K.nq);
         St* p = out + Geo::template toff<4>(tid);
 #pragma unroll
@@ -668,9 +669,9 @@ k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables ta
     GFHE_SYNC();
     if constexpr (Geo::TWO) {
         inv_round<A, 3, Geo::LO4, false>(r, TwSm<E>{tws, 16u + (tid >> 4)}, K.Ci, K.nq, Pg);
-        sm_store<4>(sm, tid, r);
+        sm_store<4, W, kColPad<W>>(sm, tid, r);
         GFHE_SYNC();
-        sm_load<8>(sm, tid, r);
+        sm_load<8, W, kColPad<W>>(sm, tid, r);
     }
     inv_round<A, 3, Geo::LO8, true>(r, TwSm<E>{tws, 1u}, K.Ci, K.nq, Pg);
     St* p = out + Geo::template toff<8>(tid);

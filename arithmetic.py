@@ -10,9 +10,21 @@
 
 Operands: torch CUDA tensors (int64/uint64, layout [L, B, N], N contiguous) are used in place;
 numpy arrays / CPU tensors are copied to the GPU and the result comes back in the same container.
-Out-of-place like the reference: inputs are never modified.  `MOD` is a scalar or one modulus per
-leading index (shape [L,1,1]).  NTT/iNTT take their moduli from the keyword-only `MOD=` or from
-the ring installed with primitive.set_ring / `with primitive.ring(...)`.  No CPU fallback.
+Out-of-place like the reference: inputs are never modified.  For vec_* `MOD` is anything numpy
+broadcasts against the operands (a scalar, one modulus per limb as [L,1,1], per batch item, per
+coefficient ...); the result has the broadcast shape.  NTT/iNTT take their moduli from the
+keyword-only `MOD=` or from the ring installed with primitive.set_ring / `with primitive.ring(...)`.
+
+Input ranges differ between the two families:
+  * vec_add / vec_sub / vec_mul accept ANY integer that fits the container (negative int64 values,
+    uint64 values up to 2^64-1, object-dtype Python ints that fit 64 bits) and return canonical
+    residues in [0, MOD) -- Python's `%` semantics, like the reference on dtype=object.
+  * NTT / iNTT (and poly_mul, poly_mul_pre, poly_mul_ntt, poly_mac_ntt, automorphism in polynomial.py)
+    require canonical residues in [0, q): the kernels' lazy-reduction schedule starts from q.
+    Centred or negative coefficients must be reduced first, e.g. x = vec_add(x, 0 * x, MOD).
+    GFHE_CHECK_RANGE=1 in the environment turns on a (slow) check that raises ValueError instead of
+    returning wrong residues.
+No CPU fallback.
 """
 import importlib.util as _ilu
 import os as _os

@@ -24,6 +24,11 @@ SYMBOLS = {
     "gfhe_plan_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, u32, u32, u64p, u64p]),
     "gfhe_plan_destroy": (ctypes.c_int, [vp]),
     "gfhe_plan_info": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(u32), ctypes.POINTER(u32)]),
+    "gfhe_plan_moduli": (ctypes.c_int, [vp, u64p, u64p, u32]),
+    "gfhe_plan_export_bytes": (ctypes.c_size_t, [vp]),
+    "gfhe_plan_export": (ctypes.c_int, [vp, vp, ctypes.c_size_t]),
+    "gfhe_plan_import": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, vp, ctypes.c_size_t]),
+    "gfhe_host_stats": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_double), u32]),
     "gfhe_ntt_forward": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_ntt_inverse": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_poly_mul_workspace_bytes": (ctypes.c_size_t, [vp, u32, u32]),
@@ -31,6 +36,9 @@ SYMBOLS = {
     "gfhe_vec_add": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_sub": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_mul": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_vec_add_u64": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_vec_sub_u64": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
+    "gfhe_vec_mul_u64": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_poly_mul_pre": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
     "gfhe_ntt_forward_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_ntt_inverse_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
@@ -68,7 +76,7 @@ for _name, (_res, _args) in SYMBOLS.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 if lib.gfhe_abi_version() != ABI_VERSION:
     raise ImportError("gpufhe_b200: ABI version mismatch (library %d, binding %d)" % (lib.gfhe_abi_version(), ABI_VERSION))
 

@@ -2,7 +2,9 @@
 // host-buffer entry points that pipeline H2D -> kernels -> D2H over limb groups.
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
+#include <thread>
 #include <vector>
 #include "../../include/gpufhe_b200.h"
 #include "plan.h"
@@ -20,12 +22,9 @@ static int check_range(const Plan* pl, uint32_t limb0, uint32_t nl) {
     return 0;
 }
 
-// The kernels are launched on the plan's device whatever the caller's current device is.
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
+// The transform / product kernels move residues with 16-byte vector accesses and TMA bulk copies: a buffer that is not
+// 16-byte aligned would raise a misaligned-address fault, which is a sticky context error.  Refuse it here instead.
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 extern "C" {
 
@@ -46,6 +45,8 @@ const char* gfhe_error_string(int code) {
         case GFHE_ETERMS: return "too many terms: terms * q^2 must fit 128 bits";
         case GFHE_EGALOIS: return "Galois element must be odd";
         case GFHE_ELAYOUT: return "packed 32-bit layout needs every modulus of the plan below 2^30";
+        case GFHE_EALIGN: return "device buffer is not 16-byte aligned (transforms and products use 16-byte accesses)";
+        case GFHE_EFORMAT: return "not a gpufhe_b200 plan image (bad magic, version, size or checksum)";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown gpufhe_b200 error";
     }
 }
@@ -60,6 +61,29 @@ int gfhe_plan_create(gfhe_plan_t* out, int device, uint32_t log2_n, uint32_t num
 }
 
 int gfhe_plan_destroy(gfhe_plan_t plan) { return plan_destroy(P(plan)); }
+
+size_t gfhe_plan_export_bytes(gfhe_plan_t plan) { return plan ? plan_image_bytes(*P(plan)) : 0; }
+int gfhe_plan_export(gfhe_plan_t plan, void* buf, size_t bytes) {
+    if (!plan || !buf) return GFHE_EARG;
+    return plan_export(*P(plan), buf, bytes);
+}
+int gfhe_plan_import(gfhe_plan_t* out, int device, const void* buf, size_t bytes) {
+    if (!out || !buf) return GFHE_EARG;
+    Plan* pl = nullptr;
+    int rc = plan_import(&pl, device, buf, bytes);
+    if (rc == 0) *out = reinterpret_cast<gfhe_plan_t>(pl);
+    return rc;
+}
+int gfhe_plan_moduli(gfhe_plan_t plan, uint64_t* moduli, uint64_t* psi, uint32_t n) {
+    if (!plan) return GFHE_EARG;
+    const Plan* pl = P(plan);
+    uint32_t k = 0;
+    for (; k < n && k < pl->L; ++k) {
+        if (moduli) moduli[k] = pl->moduli[k];
+        if (psi) psi[k] = pl->logN ? pl->psi[k] : 0;
+    }
+    return (int)k;
+}
 
 int gfhe_plan_info(gfhe_plan_t plan, int* device, uint32_t* log2_n, uint32_t* num_limbs) {
     if (!plan) return GFHE_EARG;
@@ -110,6 +134,7 @@ int gfhe_ntt_forward(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t bat
                      const uint64_t* d_in, uint64_t* d_out, void* stream) {
     if (int rc = check_range(P(plan), limb0, nl)) return rc;
     if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    if (!aligned16(d_in) || !aligned16(d_out)) return GFHE_EALIGN;
     if (P(plan)->logN == 0) return GFHE_ENOTABLES;
     DeviceGuard g(P(plan)->device);
     return (int)launch_ntt_fwd(*P(plan), limb0, nl, (const u64*)d_in, (u64*)d_out, batch, S(stream));
@@ -119,6 +144,7 @@ int gfhe_ntt_inverse(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t bat
                      const uint64_t* d_in, uint64_t* d_out, void* stream) {
     if (int rc = check_range(P(plan), limb0, nl)) return rc;
     if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    if (!aligned16(d_in) || !aligned16(d_out)) return GFHE_EALIGN;
     if (P(plan)->logN == 0) return GFHE_ENOTABLES;
     DeviceGuard g(P(plan)->device);
     return (int)launch_ntt_inv(*P(plan), limb0, nl, (const u64*)d_in, (u64*)d_out, batch, S(stream));
@@ -136,6 +162,7 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
     if (!d_a || !d_b || !d_c || batch == 0) return GFHE_EARG;
     if (P(plan)->logN == 0) return GFHE_ENOTABLES;
     if (d_c == d_a || d_c == d_b) return GFHE_EARG;
+    if (!aligned16(d_a) || !aligned16(d_b) || !aligned16(d_c) || !aligned16(d_ws)) return GFHE_EALIGN;
     const size_t need = poly_mul_workspace_bytes(*P(plan), nl, batch);
     if (need && (!d_ws || ws_bytes < need)) return GFHE_EWORKSPACE;
     DeviceGuard g(P(plan)->device);
@@ -149,6 +176,7 @@ int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t ba
     if (!d_a || !d_b_ntt || !d_c || batch == 0) return GFHE_EARG;
     if (P(plan)->logN == 0) return GFHE_ENOTABLES;
     if (d_c == d_a || d_c == d_b_ntt) return GFHE_EARG;
+    if (!aligned16(d_a) || !aligned16(d_b_ntt) || !aligned16(d_c)) return GFHE_EALIGN;
     DeviceGuard g(P(plan)->device);
     return (int)launch_poly_mul_pre(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b_ntt, (u64*)d_c, batch, S(stream));
 }
@@ -164,6 +192,7 @@ int gfhe_ntt_forward_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t
                          const uint32_t* d_in, uint32_t* d_out, void* stream) {
     if (int rc = check_packed(P(plan), limb0, nl)) return rc;
     if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    if (!aligned16(d_in) || !aligned16(d_out)) return GFHE_EALIGN;
     DeviceGuard g(P(plan)->device);
     return (int)launch_ntt_fwd_u32(*P(plan), limb0, nl, d_in, d_out, batch, S(stream));
 }
@@ -172,6 +201,7 @@ int gfhe_ntt_inverse_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t
                          const uint32_t* d_in, uint32_t* d_out, void* stream) {
     if (int rc = check_packed(P(plan), limb0, nl)) return rc;
     if (!d_in || !d_out || batch == 0) return GFHE_EARG;
+    if (!aligned16(d_in) || !aligned16(d_out)) return GFHE_EALIGN;
     DeviceGuard g(P(plan)->device);
     return (int)launch_ntt_inv_u32(*P(plan), limb0, nl, d_in, d_out, batch, S(stream));
 }
@@ -182,6 +212,7 @@ int gfhe_poly_mul_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t ba
     if (int rc = check_packed(P(plan), limb0, nl)) return rc;
     if (!d_a || !d_b || !d_c || batch == 0) return GFHE_EARG;
     if (d_c == d_a || d_c == d_b) return GFHE_EARG;
+    if (!aligned16(d_a) || !aligned16(d_b) || !aligned16(d_c) || !aligned16(d_ws)) return GFHE_EALIGN;
     const size_t need = poly_mul_workspace_bytes(*P(plan), nl, batch) / 2;   // one operand-sized scratch of 32-bit words
     if (need && (!d_ws || ws_bytes < need)) return GFHE_EWORKSPACE;
     DeviceGuard g(P(plan)->device);
@@ -193,6 +224,7 @@ int gfhe_poly_mul_pre_u32(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_
     if (int rc = check_packed(P(plan), limb0, nl)) return rc;
     if (!d_a || !d_b_ntt || !d_c || batch == 0) return GFHE_EARG;
     if (d_c == d_a || d_c == d_b_ntt) return GFHE_EARG;
+    if (!aligned16(d_a) || !aligned16(d_b_ntt) || !aligned16(d_c)) return GFHE_EALIGN;
     DeviceGuard g(P(plan)->device);
     return (int)launch_poly_mul_pre_u32(*P(plan), limb0, nl, d_a, d_b_ntt, d_c, batch, S(stream));
 }
@@ -267,21 +299,34 @@ static int vec_op(int op, gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint64_
 int gfhe_vec_add(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int64_t* a, const int64_t* b, int64_t* o, void* s) { return vec_op(0, p, l0, nl, inner, a, b, o, s); }
 int gfhe_vec_sub(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int64_t* a, const int64_t* b, int64_t* o, void* s) { return vec_op(1, p, l0, nl, inner, a, b, o, s); }
 int gfhe_vec_mul(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const int64_t* a, const int64_t* b, int64_t* o, void* s) { return vec_op(2, p, l0, nl, inner, a, b, o, s); }
+int gfhe_vec_add_u64(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const uint64_t* a, const uint64_t* b, uint64_t* o, void* s) { return vec_op(4, p, l0, nl, inner, (const int64_t*)a, (const int64_t*)b, (int64_t*)o, s); }
+int gfhe_vec_sub_u64(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const uint64_t* a, const uint64_t* b, uint64_t* o, void* s) { return vec_op(5, p, l0, nl, inner, (const int64_t*)a, (const int64_t*)b, (int64_t*)o, s); }
+int gfhe_vec_mul_u64(gfhe_plan_t p, uint32_t l0, uint32_t nl, uint64_t inner, const uint64_t* a, const uint64_t* b, uint64_t* o, void* s) { return vec_op(6, p, l0, nl, inner, (const int64_t*)a, (const int64_t*)b, (int64_t*)o, s); }
 
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------
 // host-buffer pipeline: limb groups flow H2D (stream 0) -> kernels (stream 1) -> D2H (stream 2)
-// through two device slots, so PCIe in, compute and PCIe out overlap.
+// through three device slots, so PCIe in, compute and PCIe out overlap.
+//
+// Pinned host arrays (cudaHostAlloc / torch pin_memory) are copied straight from / to the caller's
+// pointers.  Pageable arrays -- what a numpy caller of the reference actually holds -- would make
+// cudaMemcpyAsync synchronous and serialise the three streams, so they are staged through an
+// internal ring of pinned buffers (one per slot and operand): a few host threads copy group g+1 into
+// its staging buffers while group g crosses PCIe, and drain finished results the same way.
 // ------------------------------------------------------------------------------------------------
 namespace gfhe {
 
 struct HostPipe {
-    static constexpr int kSlots = 2;
+    static constexpr int kSlots = 3;
     cudaStream_t s_in = nullptr, s_run = nullptr, s_out = nullptr;
     cudaEvent_t in_done[kSlots] = {}, run_done[kSlots] = {}, out_done[kSlots] = {};
-    u64* buf[kSlots][4] = {};   // a, b, c, workspace
-    size_t cap = 0;             // bytes per buffer
+    u64* buf[kSlots][4] = {};   // device: a, b, c, workspace
+    size_t cap = 0;             // bytes per device buffer
+    u64* pin[kSlots][3] = {};   // pinned staging (pageable callers only): a, b, c
+    size_t pin_cap = 0;
+    std::vector<cudaEvent_t> tev;   // timing events, six per group: H2D / kernels / D2H begin and end
+    double stats[GFHE_HOST_STATS_N] = {};
 };
 
 void host_pipe_destroy(Plan* p) {
@@ -289,10 +334,12 @@ void host_pipe_destroy(Plan* p) {
     if (!hp) return;
     for (int s = 0; s < HostPipe::kSlots; ++s) {
         for (int k = 0; k < 4; ++k) if (hp->buf[s][k]) cudaFree(hp->buf[s][k]);
+        for (int k = 0; k < 3; ++k) if (hp->pin[s][k]) cudaFreeHost(hp->pin[s][k]);
         if (hp->in_done[s]) cudaEventDestroy(hp->in_done[s]);
         if (hp->run_done[s]) cudaEventDestroy(hp->run_done[s]);
         if (hp->out_done[s]) cudaEventDestroy(hp->out_done[s]);
     }
+    for (cudaEvent_t e : hp->tev) cudaEventDestroy(e);
     if (hp->s_in) cudaStreamDestroy(hp->s_in);
     if (hp->s_run) cudaStreamDestroy(hp->s_run);
     if (hp->s_out) cudaStreamDestroy(hp->s_out);
@@ -300,7 +347,7 @@ void host_pipe_destroy(Plan* p) {
     p->host_pipe = nullptr;
 }
 
-static cudaError_t host_pipe_get(Plan* p, size_t bytes, HostPipe** out) {
+static cudaError_t host_pipe_get(Plan* p, size_t bytes, bool need_ws, bool staged, size_t ngroups, HostPipe** out) {
     HostPipe* hp = static_cast<HostPipe*>(p->host_pipe);
     cudaError_t e = cudaSuccess;
     if (!hp) {
@@ -324,8 +371,49 @@ static cudaError_t host_pipe_get(Plan* p, size_t bytes, HostPipe** out) {
             }
         hp->cap = bytes;
     }
+    (void)need_ws;
+    if (staged && hp->pin_cap < bytes) {
+        for (int s = 0; s < HostPipe::kSlots; ++s)
+            for (int k = 0; k < 3; ++k) {
+                if (hp->pin[s][k]) cudaFreeHost(hp->pin[s][k]);
+                hp->pin[s][k] = nullptr;
+                if ((e = cudaHostAlloc(&hp->pin[s][k], bytes, cudaHostAllocDefault))) { hp->pin_cap = 0; return e; }
+            }
+        hp->pin_cap = bytes;
+    }
+    while (hp->tev.size() < 6 * ngroups) {
+        cudaEvent_t ev;
+        if ((e = cudaEventCreate(&ev))) return e;
+        hp->tev.push_back(ev);
+    }
     *out = hp;
     return cudaSuccess;
+}
+
+// true when the driver can DMA straight from / to p (pinned or managed); false for plain pageable memory
+static bool host_ptr_is_pinned(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+// memcpy split over a few host threads (one core moves ~10 GB/s; PCIe Gen5 x16 wants ~50)
+static void par_memcpy(void* dst, const void* src, size_t bytes, unsigned nthr) {
+    if (nthr <= 1 || bytes < (4u << 20)) { std::memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> pool;
+    const size_t chunk = ((bytes / nthr) + 4095) & ~(size_t)4095;
+    for (unsigned t = 1; t < nthr; ++t) {
+        const size_t o = (size_t)t * chunk;
+        if (o >= bytes) break;
+        const size_t n = bytes - o < chunk ? bytes - o : chunk;
+        pool.emplace_back([=]() { std::memcpy((char*)dst + o, (const char*)src + o, n); });
+    }
+    std::memcpy(dst, src, chunk < bytes ? chunk : bytes);
+    for (auto& th : pool) th.join();
+}
+
+static inline double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
 // op: 0 forward NTT, 1 inverse NTT, 2 poly-mul
@@ -333,6 +421,7 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     if (!pl || !h_a || !h_c || batch == 0 || (op == 2 && !h_b)) return GFHE_EARG;
     if (pl->logN == 0) return GFHE_ENOTABLES;
     DeviceGuard g(pl->device);
+    const double t_begin = now_ms();
     const size_t limb_bytes = ((size_t)batch * sizeof(u64)) << pl->logN;
     // limb groups of ~32 MiB per operand: large enough for full PCIe rate, small enough to overlap
     size_t group_mib = 32;
@@ -340,44 +429,100 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     u32 gl = (u32)(((group_mib << 20) + limb_bytes - 1) / limb_bytes);
     if (gl < 1) gl = 1;
     if (gl > pl->L) gl = pl->L;
-    HostPipe* hp = nullptr;
-    cudaError_t e = host_pipe_get(pl, limb_bytes * gl, &hp);
-    if (e) return (int)e;
+    // pageable operands are staged through pinned buffers (GFHE_HOST_STAGING=0 hands them to the driver as they are)
+    bool staged = !(host_ptr_is_pinned(h_a) && host_ptr_is_pinned(h_c) && (op != 2 || host_ptr_is_pinned(h_b)));
+    if (const char* env = std::getenv("GFHE_HOST_STAGING")) if (env[0] == '0') staged = false;
+    unsigned nthr = 4;
+    if (const char* env = std::getenv("GFHE_HOST_COPY_THREADS")) { const long v = std::atol(env); if (v >= 1 && v <= 64) nthr = (unsigned)v; }
     const size_t limb_elems = (size_t)batch << pl->logN;
     // group schedule: full groups, then a halving tail (gl/2, gl/4, ..., 1) so that what is left after the last H2D
     // copy -- the last group's kernels and its D2H copy -- is one limb's worth, not a full group's
-    std::vector<u32> groups;
+    std::vector<u32> groups, first;
     {
-        u32 left = pl->L;
-        while (left > gl) { groups.push_back(gl); left -= gl; }
-        for (u32 g = left; left > 0;) { g = g > 1 ? (g + 1) / 2 : 1; if (g > left) g = left; groups.push_back(g); left -= g; }
+        u32 left = pl->L, l0 = 0;
+        while (left > gl) { groups.push_back(gl); first.push_back(l0); l0 += gl; left -= gl; }
+        for (u32 gsz = left; left > 0;) { gsz = gsz > 1 ? (gsz + 1) / 2 : 1; if (gsz > left) gsz = left; groups.push_back(gsz); first.push_back(l0); l0 += gsz; left -= gsz; }
     }
-    int slot = 0;
-    u32 l0 = 0;
-    for (size_t it = 0; it < groups.size(); l0 += groups[it], ++it, slot ^= 1) {
-        const u32 nl = groups[it];
-        const size_t bytes = limb_bytes * nl, off = limb_elems * l0;
-        u64 *da = hp->buf[slot][0], *db = hp->buf[slot][1], *dc = hp->buf[slot][2], *dw = hp->buf[slot][3];
-        if (it >= 2) {   // slot reuse: inputs may be overwritten once its kernels ran, output once copied out
-            if ((e = cudaStreamWaitEvent(hp->s_in, hp->run_done[slot], 0))) return (int)e;
-            if ((e = cudaStreamWaitEvent(hp->s_run, hp->out_done[slot], 0))) return (int)e;
+    HostPipe* hp = nullptr;
+    cudaError_t e = host_pipe_get(pl, limb_bytes * gl, op == 2, staged, groups.size(), &hp);
+    if (e) return (int)e;
+    constexpr int kS = HostPipe::kSlots;
+    double stage_in_ms = 0, stage_out_ms = 0;
+    auto drain = [&](size_t it) -> cudaError_t {   // staged mode: group `it`'s result from its pinned slot to the caller's array
+        const int slot = (int)(it % kS);
+        if (cudaError_t de = cudaEventSynchronize(hp->out_done[slot])) return de;
+        const double t0 = now_ms();
+        par_memcpy(h_c + limb_elems * first[it], hp->pin[slot][2], limb_bytes * groups[it], nthr);
+        stage_out_ms += now_ms() - t0;
+        return cudaSuccess;
+    };
+    size_t issued = 0, drained = 0;
+    auto body = [&]() -> cudaError_t {
+        for (size_t it = 0; it < groups.size(); ++it) {
+            const int slot = (int)(it % kS);
+            const u32 nl = groups[it], l0 = first[it];
+            const size_t bytes = limb_bytes * nl, off = limb_elems * l0;
+            u64 *da = hp->buf[slot][0], *db = hp->buf[slot][1], *dc = hp->buf[slot][2], *dw = hp->buf[slot][3];
+            const u64 *src_a = h_a + off, *src_b = h_b ? h_b + off : nullptr;
+            u64* dst_c = h_c + off;
+            if (staged) {
+                if (it >= (size_t)kS) { if ((e = drain(it - kS))) return e; drained = it - kS + 1; }   // frees the slot's three staging buffers
+                const double t0 = now_ms();
+                par_memcpy(hp->pin[slot][0], src_a, bytes, nthr);
+                if (op == 2) par_memcpy(hp->pin[slot][1], src_b, bytes, nthr);
+                stage_in_ms += now_ms() - t0;
+                src_a = hp->pin[slot][0]; src_b = hp->pin[slot][1]; dst_c = hp->pin[slot][2];
+            }
+            if (it >= (size_t)kS) {   // slot reuse: inputs may be overwritten once its kernels ran, output once copied out
+                if ((e = cudaStreamWaitEvent(hp->s_in, hp->run_done[slot], 0))) return e;
+                if ((e = cudaStreamWaitEvent(hp->s_run, hp->out_done[slot], 0))) return e;
+            }
+            cudaEvent_t* tv = hp->tev.data() + 6 * it;
+            if ((e = cudaEventRecord(tv[0], hp->s_in))) return e;
+            if ((e = cudaMemcpyAsync(da, src_a, bytes, cudaMemcpyHostToDevice, hp->s_in))) return e;
+            if (op == 2 && (e = cudaMemcpyAsync(db, src_b, bytes, cudaMemcpyHostToDevice, hp->s_in))) return e;
+            if ((e = cudaEventRecord(tv[1], hp->s_in))) return e;
+            if ((e = cudaEventRecord(hp->in_done[slot], hp->s_in))) return e;
+            if ((e = cudaStreamWaitEvent(hp->s_run, hp->in_done[slot], 0))) return e;
+            if ((e = cudaEventRecord(tv[2], hp->s_run))) return e;
+            if (op == 0) e = launch_ntt_fwd(*pl, l0, nl, da, dc, batch, hp->s_run);
+            else if (op == 1) e = launch_ntt_inv(*pl, l0, nl, da, dc, batch, hp->s_run);
+            else e = launch_poly_mul(*pl, l0, nl, da, db, dc, dw, batch, hp->s_run);
+            if (e) return e;
+            if ((e = cudaEventRecord(tv[3], hp->s_run))) return e;
+            if ((e = cudaEventRecord(hp->run_done[slot], hp->s_run))) return e;
+            if ((e = cudaStreamWaitEvent(hp->s_out, hp->run_done[slot], 0))) return e;
+            if ((e = cudaEventRecord(tv[4], hp->s_out))) return e;
+            if ((e = cudaMemcpyAsync(dst_c, dc, bytes, cudaMemcpyDeviceToHost, hp->s_out))) return e;
+            if ((e = cudaEventRecord(tv[5], hp->s_out))) return e;
+            if ((e = cudaEventRecord(hp->out_done[slot], hp->s_out))) return e;
+            issued = it + 1;
         }
-        if ((e = cudaMemcpyAsync(da, h_a + off, bytes, cudaMemcpyHostToDevice, hp->s_in))) return (int)e;
-        if (op == 2 && (e = cudaMemcpyAsync(db, h_b + off, bytes, cudaMemcpyHostToDevice, hp->s_in))) return (int)e;
-        if ((e = cudaEventRecord(hp->in_done[slot], hp->s_in))) return (int)e;
-        if ((e = cudaStreamWaitEvent(hp->s_run, hp->in_done[slot], 0))) return (int)e;
-        if (op == 0) e = launch_ntt_fwd(*pl, l0, nl, da, dc, batch, hp->s_run);
-        else if (op == 1) e = launch_ntt_inv(*pl, l0, nl, da, dc, batch, hp->s_run);
-        else e = launch_poly_mul(*pl, l0, nl, da, db, dc, dw, batch, hp->s_run);
-        if (e) return (int)e;
-        if ((e = cudaEventRecord(hp->run_done[slot], hp->s_run))) return (int)e;
-        if ((e = cudaStreamWaitEvent(hp->s_out, hp->run_done[slot], 0))) return (int)e;
-        if ((e = cudaMemcpyAsync(h_c + off, dc, bytes, cudaMemcpyDeviceToHost, hp->s_out))) return (int)e;
-        if ((e = cudaEventRecord(hp->out_done[slot], hp->s_out))) return (int)e;
-    }
-    if ((e = cudaStreamSynchronize(hp->s_out))) return (int)e;
-    if ((e = cudaStreamSynchronize(hp->s_run))) return (int)e;
-    if ((e = cudaStreamSynchronize(hp->s_in))) return (int)e;
+        if (staged) for (; drained < groups.size(); ++drained) if ((e = drain(drained))) return e;
+        return cudaSuccess;
+    };
+    e = body();
+    // success or not, nothing of this call may still be in flight on the caller's buffers when it returns
+    const cudaError_t e1 = cudaStreamSynchronize(hp->s_out), e2 = cudaStreamSynchronize(hp->s_run), e3 = cudaStreamSynchronize(hp->s_in);
+    if (e == cudaSuccess) e = e1 ? e1 : (e2 ? e2 : e3);
+    if (e) return (int)e;
+    double busy[3] = {0, 0, 0};
+    for (size_t it = 0; it < issued; ++it)
+        for (int k = 0; k < 3; ++k) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, hp->tev[6 * it + 2 * k], hp->tev[6 * it + 2 * k + 1]) == cudaSuccess) busy[k] += ms;
+        }
+    const double total = (double)limb_bytes * pl->L;
+    hp->stats[GFHE_HOST_STAT_H2D_MS] = busy[0];
+    hp->stats[GFHE_HOST_STAT_KERNEL_MS] = busy[1];
+    hp->stats[GFHE_HOST_STAT_D2H_MS] = busy[2];
+    hp->stats[GFHE_HOST_STAT_H2D_BYTES] = total * (op == 2 ? 2 : 1);
+    hp->stats[GFHE_HOST_STAT_D2H_BYTES] = total;
+    hp->stats[GFHE_HOST_STAT_WALL_MS] = now_ms() - t_begin;
+    hp->stats[GFHE_HOST_STAT_STAGE_IN_MS] = stage_in_ms;
+    hp->stats[GFHE_HOST_STAT_STAGE_OUT_MS] = stage_out_ms;
+    hp->stats[GFHE_HOST_STAT_STAGED] = staged ? 1.0 : 0.0;
+    hp->stats[GFHE_HOST_STAT_GROUPS] = (double)groups.size();
     return 0;
 }
 
@@ -389,5 +534,12 @@ int gfhe_ntt_host(gfhe_plan_t plan, int inverse, uint32_t batch, const uint64_t*
 }
 int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c) {
     return run_host(P(plan), 2, batch, (const u64*)h_a, (const u64*)h_b, (u64*)h_c);
+}
+int gfhe_host_stats(gfhe_plan_t plan, double* out, uint32_t n) {
+    if (!plan || !out) return GFHE_EARG;
+    const HostPipe* hp = static_cast<const HostPipe*>(P(plan)->host_pipe);
+    uint32_t k = 0;
+    for (; k < n && k < GFHE_HOST_STATS_N; ++k) out[k] = hp ? hp->stats[k] : 0.0;
+    return (int)k;
 }
 }

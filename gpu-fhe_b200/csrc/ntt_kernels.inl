@@ -700,12 +700,12 @@ template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
 static cudaError_t launch_row_polymul(const Plan& pl, u32 limb0, const typename A::store* a, const typename A::store* b, typename A::store* c, u32 B, unsigned nt,
                                       cudaStream_t st) {
     const size_t smem = MulSmem<A, LOGT, false>::kBytes;
-    static bool configured[64] = {};   // per template instantiation, per device
+    static std::atomic<bool> configured[64];   // per template instantiation, per device (zero-initialised; setting the attribute twice is harmless)
     const int dev = pl.device & 63;
-    if (!configured[dev] && smem > 48 * 1024) {
+    if (smem > 48 * 1024 && !configured[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(k_row_polymul<A, LOGS, LOGT, WHOLE, BNTT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured[dev] = true;
+        configured[dev].store(true, std::memory_order_release);
     }
     { ProfScope ps(pl, K_ROW_POLYMUL, st); k_row_polymul<A, LOGS, LOGT, WHOLE, BNTT><<<nt, TileGeo<LOGT>::NT, smem, st>>>(a, b, c, fwd_tables(pl), inv_tables(pl), pl.logN, B, limb0); }
     return cudaGetLastError();

@@ -82,8 +82,15 @@ static cudaError_t launch_vec32(const Plan& pl, u32 limb0, u32 nl, const int* a,
 
 cudaError_t launch_vec_op_u32(int op, const Plan& pl, u32 limb0, u32 nl, const int* a, const int* b, int* out, u64 inner,
                               cudaStream_t st) {
-    if (nl == 0 || nl > 65535 || !pl.w32) return cudaErrorInvalidValue;
+    if (nl == 0 || !pl.w32) return cudaErrorInvalidValue;
     if (inner == 0) return cudaSuccess;
+    if (nl > 65535u) {   // grid.y limit: one launch per 65535 moduli
+        for (u32 l = 0; l < nl; l += 65535u) {
+            const u32 n = nl - l < 65535u ? nl - l : 65535u;
+            if (cudaError_t e = launch_vec_op_u32(op, pl, limb0 + l, n, a + (u64)l * inner, b + (u64)l * inner, out + (u64)l * inner, inner, st)) return e;
+        }
+        return cudaSuccess;
+    }
     switch (op) {
         case 0: return launch_vec32<0>(pl, limb0, nl, a, b, out, inner, st);
         case 1: return launch_vec32<1>(pl, limb0, nl, a, b, out, inner, st);

@@ -106,10 +106,15 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
             if (h_powmod(psi[l], N, q) != q - 1) return -5;                   // psi^N = -1
         }
     }
-    cudaError_t e = cudaSetDevice(device);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess) return (int)e;
+    if (device < 0 || device >= ndev) return (int)cudaErrorInvalidDevice;
+    DeviceGuard guard(device);   // the caller's current device is restored on every return path
     Plan* pl = new Plan();
     pl->device = device; pl->logN = logN; pl->L = L;
+    pl->moduli.assign(moduli, moduli + L);
+    if (logN) pl->psi.assign(psi, psi + L);
 
     pl->lazy = true;
     for (u32 l = 0; l < L; ++l) { const u32 k = 64 - (u32)__builtin_clzll(moduli[l]); if (k > pl->max_bits) pl->max_bits = k; }
@@ -173,6 +178,103 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     return 0;
 }
 
+// ---- plan image: save / load of the table cache ---------------------------------------------------
+namespace {
+struct ImageHeader {
+    char magic[8];          // "GFHEPLN" + format version
+    u32 logN, L;
+    u32 flags;              // bit 0 w32, bit 1 f64, bit 2 lazy: the arithmetic policy the tables are laid out for
+    u32 max_bits;
+    u64 table_bytes;        // bytes of d_fwd (= d_inv), all limbs
+    u64 t0_bytes;           // bytes of d_fwd_t0 (= d_inv_t0)
+    u64 payload_bytes;      // everything after the header
+    u64 checksum;           // FNV-1a over the payload, 8 bytes at a time
+};
+static_assert(sizeof(ImageHeader) == 56, "plan image header layout");
+const char kMagic[8] = {'G', 'F', 'H', 'E', 'P', 'L', 'N', '2'};
+
+u64 fnv64(const unsigned char* p, size_t n) {
+    u64 h = 1469598103934665603ull;
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) { u64 w; std::memcpy(&w, p + i, 8); h = (h ^ w) * 1099511628211ull; }
+    for (; i < n; ++i) h = (h ^ p[i]) * 1099511628211ull;
+    return h;
+}
+size_t table_bytes_of(const Plan& pl) { return pl.logN ? (sizeof(ulonglong2) << pl.logN) * pl.L / (pl.w32 ? 2 : 1) : 0; }
+size_t t0_bytes_of(const Plan& pl) { return pl.logN ? sizeof(ulonglong2) * t0_entries((size_t)1 << pl.logN) * pl.L / (pl.w32 ? 2 : 1) : 0; }
+}  // namespace
+
+size_t plan_image_bytes(const Plan& pl) {
+    return sizeof(ImageHeader) + sizeof(u64) * pl.L * 2 + sizeof(LimbParams) * pl.L + 2 * table_bytes_of(pl) + 2 * t0_bytes_of(pl);
+}
+
+int plan_export(const Plan& pl, void* buf, size_t bytes) {
+    if (!buf) return -1;
+    const size_t need = plan_image_bytes(pl);
+    if (bytes < need) return -8;
+    DeviceGuard guard(pl.device);
+    ImageHeader h{};
+    std::memcpy(h.magic, kMagic, 8);
+    h.logN = pl.logN; h.L = pl.L; h.max_bits = pl.max_bits;
+    h.flags = (pl.w32 ? 1u : 0u) | (pl.f64 ? 2u : 0u) | (pl.lazy ? 4u : 0u);
+    h.table_bytes = table_bytes_of(pl); h.t0_bytes = t0_bytes_of(pl);
+    h.payload_bytes = need - sizeof(ImageHeader);
+    unsigned char* p = static_cast<unsigned char*>(buf) + sizeof(ImageHeader);
+    std::memcpy(p, pl.moduli.data(), sizeof(u64) * pl.L); p += sizeof(u64) * pl.L;
+    if (pl.logN) std::memcpy(p, pl.psi.data(), sizeof(u64) * pl.L); else std::memset(p, 0, sizeof(u64) * pl.L);
+    p += sizeof(u64) * pl.L;
+    cudaError_t e = cudaMemcpy(p, pl.d_params, sizeof(LimbParams) * pl.L, cudaMemcpyDeviceToHost); p += sizeof(LimbParams) * pl.L;
+    for (const ulonglong2* t : {pl.d_fwd, pl.d_inv}) { if (e == cudaSuccess && h.table_bytes) e = cudaMemcpy(p, t, h.table_bytes, cudaMemcpyDeviceToHost); p += h.table_bytes; }
+    for (const ulonglong2* t : {pl.d_fwd_t0, pl.d_inv_t0}) { if (e == cudaSuccess && h.t0_bytes) e = cudaMemcpy(p, t, h.t0_bytes, cudaMemcpyDeviceToHost); p += h.t0_bytes; }
+    if (e != cudaSuccess) return (int)e;
+    h.checksum = fnv64(static_cast<unsigned char*>(buf) + sizeof(ImageHeader), h.payload_bytes);
+    std::memcpy(buf, &h, sizeof h);
+    return 0;
+}
+
+int plan_import(Plan** out, int device, const void* buf, size_t bytes) {
+    if (!out || !buf) return -1;
+    if (bytes < sizeof(ImageHeader)) return -14;
+    ImageHeader h;
+    std::memcpy(&h, buf, sizeof h);
+    if (std::memcmp(h.magic, kMagic, 8) != 0 || h.L == 0 || (h.logN != 0 && (h.logN < 4 || h.logN > 20))) return -14;
+    Plan probe; probe.logN = h.logN; probe.L = h.L; probe.w32 = (h.flags & 1u) != 0;
+    if (h.table_bytes != table_bytes_of(probe) || h.t0_bytes != t0_bytes_of(probe) || sizeof(ImageHeader) + h.payload_bytes != plan_image_bytes(probe) ||
+        bytes < plan_image_bytes(probe))
+        return -14;
+    const unsigned char* p = static_cast<const unsigned char*>(buf) + sizeof(ImageHeader);
+    if (fnv64(p, h.payload_bytes) != h.checksum) return -14;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return (int)e;
+    if (device < 0 || device >= ndev) return (int)cudaErrorInvalidDevice;
+    DeviceGuard guard(device);
+    Plan* pl = new Plan();
+    pl->device = device; pl->logN = h.logN; pl->L = h.L; pl->max_bits = h.max_bits;
+    pl->w32 = (h.flags & 1u) != 0; pl->f64 = (h.flags & 2u) != 0; pl->lazy = (h.flags & 4u) != 0;   // the policy the tables were built for
+    if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
+    pl->moduli.resize(h.L); std::memcpy(pl->moduli.data(), p, sizeof(u64) * h.L); p += sizeof(u64) * h.L;
+    if (h.logN) { pl->psi.resize(h.L); std::memcpy(pl->psi.data(), p, sizeof(u64) * h.L); }
+    p += sizeof(u64) * h.L;
+    for (u32 l = 0; l < h.L; ++l) {   // the constants must belong to the moduli the header names
+        LimbParams lp; std::memcpy(&lp, p + sizeof(LimbParams) * l, sizeof lp);
+        if (lp.q != pl->moduli[l] || lp.q < 2 || lp.q >= (1ull << 62)) { delete pl; return -14; }
+    }
+    if ((e = cudaMalloc(&pl->d_params, sizeof(LimbParams) * h.L)) == cudaSuccess) e = cudaMemcpy(pl->d_params, p, sizeof(LimbParams) * h.L, cudaMemcpyHostToDevice);
+    p += sizeof(LimbParams) * h.L;
+    for (ulonglong2** t : {&pl->d_fwd, &pl->d_inv}) {
+        if (e == cudaSuccess && h.table_bytes) { if ((e = cudaMalloc(t, h.table_bytes)) == cudaSuccess) e = cudaMemcpy(*t, p, h.table_bytes, cudaMemcpyHostToDevice); }
+        p += h.table_bytes;
+    }
+    for (ulonglong2** t : {&pl->d_fwd_t0, &pl->d_inv_t0}) {
+        if (e == cudaSuccess && h.t0_bytes) { if ((e = cudaMalloc(t, h.t0_bytes)) == cudaSuccess) e = cudaMemcpy(*t, p, h.t0_bytes, cudaMemcpyHostToDevice); }
+        p += h.t0_bytes;
+    }
+    if (e != cudaSuccess) { plan_destroy(pl); return (int)e; }
+    *out = pl;
+    return 0;
+}
+
 // ---- policy dispatch ---------------------------------------------------------------------------
 extern template struct Launcher<Harvey>;
 extern template struct Launcher<Lazy60>;
@@ -224,7 +326,7 @@ void host_pipe_destroy(Plan* p);   // capi.cu
 
 int plan_destroy(Plan* p) {
     if (!p) return 0;
-    cudaSetDevice(p->device);
+    DeviceGuard guard(p->device);
     host_pipe_destroy(p);
     if (p->prof) {
         for (auto& r : p->prof->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }

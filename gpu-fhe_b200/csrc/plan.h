@@ -35,6 +35,7 @@ struct Plan {
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
     ulonglong2* d_fwd_t0 = nullptr;    // [L][N/512][15][32] warp-tiled copy of d_fwd for the window at bit 0
     ulonglong2* d_inv_t0 = nullptr;    // [L][N/512][15][32] same for d_inv (ntt_core.cuh, TwT0)
+    std::vector<u64> moduli, psi;      // host copies (psi empty when logN == 0): what gfhe_plan_moduli / the plan image report
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
     Profiler* prof = nullptr;
 };
@@ -51,9 +52,22 @@ struct ProfScope {
     ~ProfScope() { if (p) cudaEventRecord(p->recs[idx].b, st); }
 };
 
+// The kernels (and the plan's allocations) live on the plan's device whatever the caller's current device is; the caller's
+// device is restored on scope exit, so torch's notion of the current device never changes behind its back.
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 // plan.cu
 int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi);
 int plan_destroy(Plan* p);
+// Serialisable table cache: a plan image is the header + moduli + roots + the four device
+// tables exactly as they sit in HBM, so importing it is validation + four uploads -- no root search, no table generation.
+size_t plan_image_bytes(const Plan& pl);
+int plan_export(const Plan& pl, void* buf, size_t bytes);
+int plan_import(Plan** out, int device, const void* buf, size_t bytes);
 
 // ntt_kernels.inl, instantiated per arithmetic policy by ntt_harvey.cu / ntt_lazy.cu
 template <class A>

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define GFHE_ABI_VERSION 3
+#define GFHE_ABI_VERSION 4
 
 #define GFHE_EARG      (-1)   /* null pointer / zero size */
 #define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
@@ -52,6 +52,8 @@ extern "C" {
 #define GFHE_ETERMS    (-10)  /* too many terms: terms * q^2 must fit 128 bits */
 #define GFHE_EGALOIS   (-11)  /* Galois element must be odd */
 #define GFHE_ELAYOUT   (-12)  /* packed 32-bit layout asked of a plan with a modulus >= 2^30 */
+#define GFHE_EALIGN    (-13)  /* a device buffer of a transform / product call is not 16-byte aligned */
+#define GFHE_EFORMAT   (-14)  /* gfhe_plan_import: not a plan image of this library version, or corrupted */
 
 typedef struct gfhe_plan* gfhe_plan_t;   /* opaque; one per (device, N, modulus chain) */
 
@@ -65,9 +67,22 @@ int gfhe_plan_create(gfhe_plan_t* out, int device, uint32_t log2_n, uint32_t num
                      const uint64_t* moduli, const uint64_t* psi);
 int gfhe_plan_destroy(gfhe_plan_t plan);
 int gfhe_plan_info(gfhe_plan_t plan, int* device, uint32_t* log2_n, uint32_t* num_limbs);
+/* The plan's moduli and roots (psi[l] = 0 for a plan without tables): writes min(n, num_limbs) entries, returns the count. */
+int gfhe_plan_moduli(gfhe_plan_t plan, uint64_t* moduli, uint64_t* psi, uint32_t n);
+
+/* Serialisable table cache (the reference's primitive.py:3-4 has no tables at all).
+ * gfhe_plan_export writes a self-describing image (header, moduli, roots, per-limb constants and the twiddle tables as
+ * they sit in HBM, checksummed) into a caller buffer of gfhe_plan_export_bytes(); gfhe_plan_import validates an image
+ * and uploads it to `device` -- no root search and no table generation.  GFHE_EFORMAT: not an image of this format,
+ * truncated, or corrupted; GFHE_EWORKSPACE: export buffer too small. */
+size_t gfhe_plan_export_bytes(gfhe_plan_t plan);
+int gfhe_plan_export(gfhe_plan_t plan, void* buf, size_t bytes);
+int gfhe_plan_import(gfhe_plan_t* out, int device, const void* buf, size_t bytes);
 
 /* Batched transforms over limbs [limb0, limb0 + num_limbs) of the plan; buffers are
- * [num_limbs, batch, N].  in == out is allowed.  Forward expects residues in [0, q). */
+ * [num_limbs, batch, N].  in == out is allowed.  Inputs must be canonical residues in [0, q) (both directions: the
+ * lazy-reduction range schedule starts from q); every device buffer of the transform and product calls must be
+ * 16-byte aligned (GFHE_EALIGN otherwise -- the kernels use 16-byte vector accesses and TMA bulk copies). */
 int gfhe_ntt_forward(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
                      const uint64_t* d_in, uint64_t* d_out, void* stream);
 int gfhe_ntt_inverse(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
@@ -124,6 +139,15 @@ int gfhe_vec_sub(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t 
 int gfhe_vec_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
                  const int64_t* d_a, const int64_t* d_b, int64_t* d_out, void* stream);
 
+/* The same for arrays of UNSIGNED 64-bit words (uint64 containers): values >= 2^63 are large positive numbers here,
+ * negative ones above.  Same kernels, the input reduction differs. */
+int gfhe_vec_add_u64(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, void* stream);
+int gfhe_vec_sub_u64(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, void* stream);
+int gfhe_vec_mul_u64(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint64_t inner,
+                     const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_out, void* stream);
+
 /* NTT-domain multiply-accumulate: out[l, i] = sum_{t < terms} a[t*term_stride + l*inner + i] * b[same] mod q_l.
  * a, b hold `terms` arrays of layout [num_limbs, inner] (inner = batch * N) spaced term_stride words apart; inputs
  * must be canonical residues in [0, q) (what gfhe_ntt_forward writes).  terms == 1 is the pointwise product.
@@ -138,11 +162,29 @@ int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint6
 int gfhe_automorphism(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch, uint32_t k, int ntt_domain,
                       const uint64_t* d_in, uint64_t* d_out, void* stream);
 
-/* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan
- * (pinned memory gives full PCIe rate; pageable works).  Limb groups are streamed
- * H2D -> kernels -> D2H on separate streams so copies overlap compute.  Synchronous. */
+/* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan.  Limb groups are streamed
+ * H2D -> kernels -> D2H on separate streams so copies overlap compute.  Pinned arrays are copied from / to in place;
+ * pageable arrays (plain numpy / malloc memory) are staged through an internal ring of pinned buffers by a few host
+ * threads (GFHE_HOST_COPY_THREADS, default 4), so the three streams still overlap.  Synchronous: nothing is in flight
+ * on the caller's buffers when the call returns, on error paths included. */
 int gfhe_ntt_host(gfhe_plan_t plan, int inverse, uint32_t batch, const uint64_t* h_in, uint64_t* h_out);
 int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c);
+
+/* What the last gfhe_*_host call on this plan spent where: out[k] for k < min(n, GFHE_HOST_STATS_N), returns the count.
+ * The *_MS entries of the copies and kernels are stream-busy times summed over limb groups (CUDA events around each
+ * group's copies / launches), so bytes / ms is the rate each direction actually ran at. */
+#define GFHE_HOST_STAT_H2D_MS       0
+#define GFHE_HOST_STAT_KERNEL_MS    1
+#define GFHE_HOST_STAT_D2H_MS       2
+#define GFHE_HOST_STAT_H2D_BYTES    3
+#define GFHE_HOST_STAT_D2H_BYTES    4
+#define GFHE_HOST_STAT_WALL_MS      5
+#define GFHE_HOST_STAT_STAGE_IN_MS  6   /* host threads copying pageable inputs into pinned staging */
+#define GFHE_HOST_STAT_STAGE_OUT_MS 7   /* ... and results out of it */
+#define GFHE_HOST_STAT_STAGED       8   /* 1 when the call staged (pageable caller), else 0 */
+#define GFHE_HOST_STAT_GROUPS       9
+#define GFHE_HOST_STATS_N           10
+int gfhe_host_stats(gfhe_plan_t plan, double* out, uint32_t n);
 
 /* Measurement hook (bench.py): when enabled, every kernel launched through `plan` is bracketed
  * by cudaEvents on its stream.  gfhe_profile_read waits for them, writes up to max_kernels

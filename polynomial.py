@@ -19,6 +19,7 @@ from arithmetic import _d
 
 __all__ = ["np", "vec_add", "vec_sub", "vec_mul", "NTT", "iNTT", "XXX",
            "find_psi", "ntt_primes", "is_probable_prime", "set_ring", "get_ring", "ring", "make_plan", "clear_plans",
+           "save_plan", "load_plan",
            "poly_add", "poly_sub", "poly_mul", "poly_mul_pre", "poly_mul_ntt", "poly_mac_ntt", "automorphism", "poly_mul_pair"]
 
 
@@ -32,7 +33,8 @@ def poly_sub(a, b, MOD):
 
 def poly_mul(a, b, MOD=None):
     """a, b: [L, B, N] (or [B, N] / [N] with a single modulus); MOD: scalar, list of L moduli, an
-    [L,1,1] array, or None to use the installed ring."""
+    [L,1,1] array, or None to use the installed ring.  Coefficients must be canonical residues in [0, q)
+    (see arithmetic.py: reduce centred / negative coefficients with vec_add first)."""
     assert a.shape == b.shape
     return _d.poly_mul(a, b, MOD)
 

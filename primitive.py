@@ -8,7 +8,8 @@ from arithmetic import _pkg
 _r = _pkg.ring
 
 __all__ = ["np", "vec_add", "vec_sub", "vec_mul", "NTT", "iNTT", "XXX",
-           "find_psi", "ntt_primes", "is_probable_prime", "set_ring", "get_ring", "ring", "make_plan", "clear_plans"]
+           "find_psi", "ntt_primes", "is_probable_prime", "set_ring", "get_ring", "ring", "make_plan", "clear_plans",
+           "save_plan", "load_plan"]
 
 find_psi = _r.find_psi                    # primitive 2N-th root of unity mod q
 ntt_primes = _r.ntt_primes                # largest `bits`-bit primes = 1 mod 2N
@@ -17,6 +18,8 @@ set_ring = _r.set_ring                    # moduli used by NTT(x)/iNTT(x) when M
 get_ring = _r.get_ring
 ring = _r.ring                            # context manager form of set_ring
 clear_plans = _r.clear_plans
+save_plan = _r.save_plan                  # serialisable table cache: plan image to a file ...
+load_plan = _r.load_plan                  # ... and back into HBM without root search or table generation
 
 
 def XXX():

@@ -34,7 +34,7 @@ def test_binding_covers_header_and_abi_version(built_lib):
     import arithmetic  # noqa: F401  (loads gpu_fhe_b200)
     from gpu_fhe_b200 import _capi
     assert set(_capi.SYMBOLS) == declared_symbols()
-    assert _capi.lib.gfhe_abi_version() == _capi.ABI_VERSION == 3
+    assert _capi.lib.gfhe_abi_version() == _capi.ABI_VERSION == 4
     assert _capi.error_string(0) == "success"
     assert "2N" in _capi.error_string(-4)
 
@@ -56,3 +56,8 @@ def test_argument_errors_need_no_gpu(built_lib):
     assert _capi.lib.gfhe_plan_create(ctypes.byref(h), 0, 4, 1, q, one) == -5          # 1 is not a 32nd root of -1
     assert _capi.lib.gfhe_ntt_forward(None, 0, 1, 1, None, None, None) == -1
     assert _capi.lib.gfhe_poly_mul_workspace_bytes(None, 1, 1) == 0
+    # plan images: garbage is refused before any CUDA call
+    assert _capi.lib.gfhe_plan_import(ctypes.byref(h), 0, b"not a plan image" * 8, 128) == -14
+    assert _capi.lib.gfhe_plan_import(ctypes.byref(h), 0, b"short", 5) == -14
+    assert _capi.lib.gfhe_plan_export_bytes(None) == 0
+    assert "aligned" in _capi.error_string(-13) and "image" in _capi.error_string(-14)

@@ -34,14 +34,37 @@ def test_xxx_prints_xxx(built_lib, capsys):
     assert capsys.readouterr().out == "XXX\n"       # /root/reference/primitive.py:3-4
 
 
-def test_roots_and_primes(built_lib):
+# (q, N, smallest base x, psi) verified there with sympy -- literals, so that neither the product
+# code's root search nor the oracle's can vouch for the other
+ROOT_LITERALS = [
+    (1073479681, 1024, 11, 530309095),
+    (1125899902124033, 4096, 3, 93790016731446),
+    (1152921504606584833, 65536, 5, 987813353222176621),
+    (1152921504606584833, 131072, 5, 720645352895426071),
+]
+
+
+@pytest.mark.parametrize("q,N,x,psi", ROOT_LITERALS)
+def test_root_literals_and_exact_order(built_lib, q, N, x, psi):
     import primitive as P
     from oracle import oracle as O
-    for q, N in [(1073479681, 1024), (1125899902124033, 4096), (1152921504606584833, 65536)]:
-        psi = P.find_psi(q, N)
-        assert psi == O.find_psi(q, N)                # product code and oracle agree on the convention
-        assert pow(psi, N, q) == q - 1
-    assert P.ntt_primes(60, 3) == O.ntt_primes(60, 3)
+    assert P.find_psi(q, N) == psi                    # product code against the literal ...
+    assert O.find_psi(q, N) == psi                    # ... and the oracle against the literal, each on its own
+    assert psi == pow(x, (q - 1) // (2 * N), q)
+    for y in range(2, x):                             # x is the SMALLEST base that works
+        assert pow(pow(y, (q - 1) // (2 * N), q), N, q) != q - 1
+    # psi has order exactly 2N: psi^(2N) = 1 and, 2N being a power of two, psi^N != 1 rules out every proper divisor
+    assert pow(psi, 2 * N, q) == 1 and pow(psi, N, q) == q - 1 != 1
+    assert len({pow(psi, k, q) for k in range(0, 2 * N, max(1, N // 64))}) == len(range(0, 2 * N, max(1, N // 64)))
+
+
+def test_roots_and_primes(built_lib):
+    import primitive as P
+    # SURVEY.md section 8d prime families (literals from there)
+    assert P.ntt_primes(60, 4) == [1152921504606584833, 1152921504598720513, 1152921504592429057, 1152921504581419009]
+    assert P.ntt_primes(60, 64)[-1] == 1152921504241942529
+    assert P.ntt_primes(50, 4) == [1125899902124033, 1125899886395393, 1125899884036097, 1125899882987521]
+    assert P.ntt_primes(30, 2) == [1073479681, 1068236801]
     assert P.ntt_primes(30, 1, N=1024) == [1073707009]    # largest 30-bit prime = 1 mod 2048
     with pytest.raises(ValueError):
         P.find_psi(101, 16)
@@ -73,11 +96,16 @@ def test_shape_and_modulus_mapping(built_lib):
     assert d._lbn((2, 3, 5, 64), 2) == (2, 15, 64)
     with pytest.raises(ValueError):
         d._lbn((3, 64), 2)
-    assert d._vec_moduli(7, (2, 3, 4)) == ((7,), 24)
-    assert d._vec_moduli(np.array([[[5]], [[7]]], dtype=object), (2, 3, 4)) == ((5, 7), 12)
-    assert d._vec_moduli(np.array([5, 7]), (2,)) == ((5, 7), 1)
-    with pytest.raises(ValueError):          # numpy would broadcast (2,) against the LAST axis
-        d._vec_moduli(np.array([5, 7]), (2, 3, 2))
+    # MOD follows numpy's broadcasting rules (/root/reference/arithmetic.py:5): (moduli, result shape, axis permutation, inner)
+    assert d._vec_moduli(7, (2, 3, 4)) == ((7,), (2, 3, 4), None, 24)
+    assert d._vec_moduli(np.array([[[5]], [[7]]], dtype=object), (2, 3, 4)) == ((5, 7), (2, 3, 4), None, 12)
+    assert d._vec_moduli(np.array([5, 7]), (2,)) == ((5, 7), (2,), None, 1)
+    assert d._vec_moduli(np.array([5, 7]), (2, 3, 2)) == ((5, 7), (2, 3, 2), [2, 0, 1], 6)          # varies along the LAST axis
+    assert d._vec_moduli(np.array([[5], [7], [11]]), (2, 3, 2)) == ((5, 7, 11), (2, 3, 2), [1, 0, 2], 4)
+    assert d._vec_moduli(np.array([[[5]], [[7]]]), (3, 4)) == ((5, 7), (2, 3, 4), None, 12)        # MOD adds an axis
+    assert d._vec_moduli(np.array([[5, 7], [11, 13]]), (2, 2)) == ((5, 7, 11, 13), (2, 2), None, 1)  # one modulus per element
+    with pytest.raises(ValueError):          # does not broadcast: numpy raises ValueError too
+        d._vec_moduli(np.array([5, 7, 11]), (2, 3, 2))
 
 
 def test_no_cpu_fallback(built_lib):
@@ -92,6 +120,38 @@ def test_no_cpu_fallback(built_lib):
             call()
     with pytest.raises(AssertionError):     # shape mismatch: bare AssertionError like arithmetic.py:4
         P.vec_add(np.arange(4), np.arange(5), 7)
+
+
+def test_object_operands_must_fit_a_word(built_lib):
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import dispatch as d
+    # exact Python ints are accepted only if they fit ONE 64-bit reading (signed or unsigned); validated before any device work
+    for bad in ([1 << 64], [-(1 << 63) - 1], [-1, 1 << 63]):
+        with pytest.raises(ValueError, match="64-bit word"):
+            d._Arg(np.array(bad, dtype=object))
+    with pytest.raises(TypeError):
+        d._Arg(np.array([0.5, 1.5]))
+
+
+def test_host_entry_points_validate_shapes(built_lib):
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import dispatch as d
+    a = np.zeros((2, 3, 16), dtype=np.uint64)
+    # the C side copies L*B*N words from / to each array: mismatched shapes must never reach it
+    with pytest.raises(AssertionError):
+        d.poly_mul_host(a, np.ascontiguousarray(a[:, :2]), a.copy(), [97, 193])
+    with pytest.raises(AssertionError):
+        d.poly_mul_host(a, a, np.zeros((2, 3, 8), dtype=np.uint64), [97, 193])
+    with pytest.raises(AssertionError):
+        d.ntt_host(a, np.zeros((2, 2, 16), dtype=np.uint64), [97, 193])
+    with pytest.raises(ValueError):                      # leading dimension is not the limb count
+        d.poly_mul_host(a, a, a.copy(), [97, 193, 257])
+    with pytest.raises(TypeError):
+        d.poly_mul_host(a.astype(np.int32), a.astype(np.int32), a.astype(np.int32), [97, 193])
+    ro = a.copy()
+    ro.flags.writeable = False
+    with pytest.raises(ValueError, match="writable"):
+        d.poly_mul_host(a, a, ro, [97, 193])
 
 
 def test_partition():

@@ -53,6 +53,7 @@ SYMBOLS = {
     "gfhe_automorphism": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),
     "gfhe_poly_mul_host": (ctypes.c_int, [vp, u32, vp, vp, vp]),
+    "gfhe_debug_pipe_schedule": (ctypes.c_int, [u32, ctypes.POINTER(u32), u32, u32, ctypes.POINTER(u32), u32, ctypes.POINTER(u32)]),
     "gfhe_profile_enable": (ctypes.c_int, [vp, ctypes.c_int]),
     "gfhe_profile_read": (ctypes.c_int, [vp, u32, ctypes.POINTER(ctypes.c_char_p), ctypes.POINTER(ctypes.c_double),
                                          ctypes.POINTER(ctypes.c_uint64)]),

@@ -7,6 +7,7 @@
 #include <thread>
 #include <vector>
 #include "../../include/gpufhe_b200.h"
+#include "pipe_sched.h"
 #include "plan.h"
 
 using namespace gfhe;
@@ -93,6 +94,16 @@ int gfhe_plan_info(gfhe_plan_t plan, int* device, uint32_t* log2_n, uint32_t* nu
     return 0;
 }
 
+int gfhe_debug_pipe_schedule(uint32_t passes, const uint32_t* tiles_per_pass, uint32_t npoly, uint32_t resident,
+                             uint32_t* out, uint32_t max_tickets, uint32_t* lag) {
+    if (!tiles_per_pass || passes < 2 || passes > 3 || npoly == 0) return GFHE_EARG;
+    const PipeSched sc = make_pipe_sched(passes, tiles_per_pass, npoly, resident);
+    if (lag) *lag = sc.lag;
+    if (out)
+        for (uint32_t t = 0; t < sc.total && t < max_tickets; ++t) pipe_decode(sc, t, out + 3 * t, out + 3 * t + 1, out + 3 * t + 2);
+    return (int)sc.total;
+}
+
 int gfhe_profile_enable(gfhe_plan_t plan, int on) {
     if (!plan) return GFHE_EARG;
     Plan* pl = P(plan);
@@ -101,7 +112,8 @@ int gfhe_profile_enable(gfhe_plan_t plan, int on) {
     return 0;
 }
 
-static const char* const kKernelNames[K_COUNT] = {"k_col_fwd", "k_row_fwd", "k_row_inv", "k_col_inv", "k_row_polymul", "k_vec", "k_mul_acc", "k_automorphism"};
+static const char* const kKernelNames[K_COUNT] = {"k_col_fwd", "k_row_fwd", "k_row_inv", "k_col_inv", "k_row_polymul", "k_vec", "k_mul_acc", "k_automorphism",
+                                                  "k_pipe_ntt_fwd", "k_pipe_ntt_inv", "k_pipe_polymul"};
 
 int gfhe_profile_read(gfhe_plan_t plan, uint32_t max_kernels, const char** names, double* total_ms, uint64_t* launches) {
     if (!plan) return GFHE_EARG;

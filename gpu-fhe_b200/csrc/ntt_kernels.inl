@@ -21,6 +21,7 @@
 #include <atomic>
 #include <cstdlib>
 #include "ntt_core.cuh"
+#include "pipe_sched.h"
 #include "plan.h"
 
 namespace gfhe {
@@ -91,9 +92,9 @@ template <class A> struct RowPf {   // k_row_inv: 30-bit inverse step 0.221 -> 0
 };
 
 template <int LOGT>
-__device__ __forceinline__ TileId tile_id(u32 logN, u32 B, u32 limb0) {
+__device__ __forceinline__ TileId tile_id(u32 tile, u32 logN, u32 B, u32 limb0) {
     TileId s;
-    s.g0 = (u64)blockIdx.x << LOGT;
+    s.g0 = (u64)tile << LOGT;
     const u32 p = (u32)(s.g0 >> logN);
     s.off = (u32)s.g0 & ((1u << logN) - 1u);
     s.limb = limb0 + p / B;
@@ -134,6 +135,11 @@ __device__ __forceinline__ void fwd_semi_all(typename A::word (&r)[kElems], cons
 #pragma unroll
     for (int i = 0; i < kElems; ++i) r[i] = fwd_semi<A>(r[i], K.q, K.nq, ks, km);
 }
+
+// CG: the words were written by another CTA of the same launch (pipelined kernels below): read them from L2, never from
+// this SM's L1, which may still hold what the same addresses held earlier in the launch.
+template <bool CG, class T>
+__device__ __forceinline__ T ld_res(const T* p) { if constexpr (CG) return __ldcg(p); else return *p; }
 
 template <int LOGT>
 __device__ __forceinline__ void copy_out_padded(const u64* sm, u64* out, u32 tid) {
@@ -229,26 +235,26 @@ __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) 
 }
 
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
-template <class A, int LOGS, int LOGT>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
-k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+// The tile bodies are device functions of the tile index: the stand-alone kernels call them with blockIdx.x, the pipelined
+// kernels at the end of this file with the tile their ticket names.
+template <class A, int LOGS, int LOGT, bool CG = false>
+__device__ __forceinline__ void row_fwd_body(const typename A::store* in, typename A::store* out, const Tables& tabs, u32 logN, u32 B, u32 limb0,
+                                             u32 tile, typename A::word* sm) {
     typedef typename A::word W;
     typedef typename A::store S;
-    __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
-    const TileId s = tile_id<LOGT>(logN, B, limb0);
+    const TileId s = tile_id<LOGT>(tile, logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const auto T = limb_tables<A>(tabs, s.limb, logN);
-    prefetch_row_tile<LOGT, RowPf<A>::kFwd>(in, tid);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
     if (A::kFloat && logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words (they differ from canonical ones for the FP64 policy only)
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, ld_res<CG>(in + s.g0 + elem_index<P0>(tid, 0) + (i << P0)), tid * 77u + i);
     } else {
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, (in + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_u64, ld_res<CG>(in + s.g0 + elem_index<P0>(tid, 0) + (i << P0)), tid * 77u + i);
     }
     slab_fwd<A, LOGS>(r, sm, tid, T, s.off, K.Cf, K.nq);
     fwd_final_all<A>(r, K, Pg);
@@ -270,19 +276,26 @@ k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs
     }
 }
 
+template <class A, int LOGS, int LOGT>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
+k_row_fwd(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[padded_words(LOGT)];
+    prefetch_row_tile<LOGT, RowPf<A>::kFwd>(in, threadIdx.x);
+    row_fwd_body<A, LOGS, LOGT>(in, out, tabs, logN, B, limb0, blockIdx.x, sm);
+}
+
 // Inverse: the LOGS low stages (bottom first).  Always the first pass of an inverse NTT; when the
 // tile is the whole polynomial it also folds N^-1 and fully reduces.
 template <class A, int LOGS, int LOGT, bool WHOLE>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
-k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+__device__ __forceinline__ void row_inv_body(const typename A::store* in, typename A::store* out, const Tables& tabs, u32 logN, u32 B, u32 limb0,
+                                             u32 tile, typename A::word* sm) {
     typedef typename A::word W;
-    __shared__ __align__(16) W sm[padded_words(LOGT)];
     const u32 tid = threadIdx.x;
-    const TileId s = tile_id<LOGT>(logN, B, limb0);
+    const TileId s = tile_id<LOGT>(tile, logN, B, limb0);
     const LimbParams* __restrict__ Pg = tabs.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const auto T = limb_tables<A>(tabs, s.limb, logN);
-    prefetch_row_tile<LOGT, RowPf<A>::kInv>(in, tid);
     W r[kElems];
     if constexpr (LOGT > 4) {
         copy_in_padded<LOGT>(sm, in + s.g0, tid);
@@ -296,6 +309,15 @@ k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs
     constexpr int P0 = Sched<LOGS>::p0(0);
 #pragma unroll
     for (int i = 0; i < kElems; ++i) (out + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);
+}
+
+template <class A, int LOGS, int LOGT, bool WHOLE>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, RowOcc<A, LOGT>::kB)
+k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs, u32 logN, u32 B, u32 limb0) {
+    typedef typename A::word W;
+    __shared__ __align__(16) W sm[padded_words(LOGT)];
+    prefetch_row_tile<LOGT, RowPf<A>::kInv>(in, threadIdx.x);
+    row_inv_body<A, LOGS, LOGT, WHOLE>(in, out, tabs, logN, B, limb0, blockIdx.x, sm);
 }
 
 // ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
@@ -337,27 +359,51 @@ __device__ __forceinline__ void tma_tile_wait(u64* mbar) {
         "}\n" ::"r"(bar) : "memory");
 }
 
+// mbarrier pieces used by the pipelined and persistent kernels: init once, then one phase per tile
+__device__ __forceinline__ void mbar_init(u64* mbar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
+}
+__device__ __forceinline__ void tma_tile_issue(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
+    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* mbar, u32 parity) {
+    const u32 bar = smem_u32(mbar);
+    u32 done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    } while (!done);
+}
+
 // Fused product on a tile: c = row-inv( row-fwd(a) .* row-fwd(b) ).  For N <= 4096 (WHOLE) this
 // is the complete negacyclic product of one limb-polynomial in a single launch.
 // BNTT: b is already in the NTT domain (canonical residues, the order gfhe_ntt_forward writes): its forward transform is
 // skipped and NTT(a) never leaves the registers -- a third of the butterflies gone for callers that cache NTT(b).
-template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
-__global__ void __launch_bounds__(TileGeo<LOGT>::NT, MulSmem<A, LOGT, false>::kMinB)
-k_row_polymul(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN, u32 B,
-              u32 limb0) {
+// PIPE: called from a pipelined kernel (end of this file): a and b were written by other CTAs of the same launch (a is read
+// through L2 only; the TMA copy of b is ordered after the dependency wait by the caller), the mbarrier was initialised once
+// at kernel start and this tile uses its phase *parity (a shared-memory word, read where the wait is).
+template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT, bool PIPE>
+__device__ __forceinline__ void row_polymul_body(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables& tf,
+                                                 const Tables& ti, u32 logN, u32 B, u32 limb0, u32 tile, unsigned char* smem, const volatile u32* parity) {
     typedef typename A::word W;
     typedef typename A::store S;
     using Lay = MulSmem<A, LOGT, false>;
-    extern __shared__ __align__(16) unsigned char smem[];
     W* sm0 = reinterpret_cast<W*>(smem);                           // exchange buffer
     W* sm1 = reinterpret_cast<W*>(smem + Lay::kOff1);              // stash for NTT(a) while NTT(b) is computed
     S* smb = reinterpret_cast<S*>(smem + Lay::kOffB);              // b's tile, fetched by one TMA bulk copy while a is transformed
     u64* mbar = reinterpret_cast<u64*>(smem + Lay::kOffBar);
     const u32 tid = threadIdx.x;
-    const TileId s = tile_id<LOGT>(logN, B, limb0);
-    if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(S) << LOGT, mbar);
-    prefetch_row_tile<LOGT, GFHE_PF_MUL>(a, tid);
-    prefetch_row_tile<LOGT, GFHE_PF_MUL>(b, tid);
+    const TileId s = tile_id<LOGT>(tile, logN, B, limb0);
+    if constexpr (PIPE) {
+        if (tid == 0) tma_tile_issue(smb, b + s.g0, (u32)sizeof(S) << LOGT, mbar);
+    } else {
+        if (tid == 0) tma_tile_load(smb, b + s.g0, (u32)sizeof(S) << LOGT, mbar);
+        prefetch_row_tile<LOGT, GFHE_PF_MUL>(a, tid);
+        prefetch_row_tile<LOGT, GFHE_PF_MUL>(b, tid);
+    }
     const LimbParams* __restrict__ Pg = tf.params + s.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
     const auto Tf = limb_tables<A>(tf, s.limb, logN);
@@ -366,12 +412,12 @@ k_row_polymul(const typename A::store* a, const typename A::store* b, typename A
     W r[kElems];
 #pragma unroll
     for (int i = 0; i < kElems; ++i)
-        r[i] = WHOLE ? GFHE_GLD(A::from_u64, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i)
-                     : GFHE_GLD(A::from_raw, (a + s.g0 + elem_index<P0>(tid, 0))[i << P0], tid * 77u + i);
+        r[i] = WHOLE ? GFHE_GLD(A::from_u64, ld_res<PIPE>(a + s.g0 + elem_index<P0>(tid, 0) + (i << P0)), tid * 77u + i)
+                     : GFHE_GLD(A::from_raw, ld_res<PIPE>(a + s.g0 + elem_index<P0>(tid, 0) + (i << P0)), tid * 77u + i);
     slab_fwd<A, LOGS, WHOLE ? 1 : 16>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);   // whole polynomial: canonical inputs
     fwd_semi_all<A>(r, K, Pg);
     if constexpr (BNTT) {
-        tma_tile_wait(mbar);
+        if constexpr (PIPE) mbar_wait(mbar, *parity); else tma_tile_wait(mbar);
         const S* pb = smb + (tid << 4);   // this thread's 16 residues of NTT(b), same positions as r[]
         if constexpr (A::kFloat) {
 #pragma unroll
@@ -406,7 +452,7 @@ k_row_polymul(const typename A::store* a, const typename A::store* b, typename A
     } else {
         sm_store<0>(sm1, tid, r);   // private row of sm1: written and read back by this thread only
         GFHE_SYNC();            // every thread has finished reading a's last exchange out of sm0 (and sees the barrier)
-        tma_tile_wait(mbar);
+        if constexpr (PIPE) mbar_wait(mbar, *parity); else tma_tile_wait(mbar);
     #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = WHOLE ? A::from_u64((smb + elem_index<P0>(tid, 0))[i << P0]) : A::from_raw((smb + elem_index<P0>(tid, 0))[i << P0]);
         slab_fwd<A, LOGS, WHOLE ? 1 : 16>(r, sm0, tid, Tf, s.off, K.Cf, K.nq);   // whole polynomial: canonical inputs
@@ -446,30 +492,20 @@ k_row_polymul(const typename A::store* a, const typename A::store* b, typename A
     for (int i = 0; i < kElems; ++i) (c + s.g0 + elem_index<P0>(tid, 0))[i << P0] = WHOLE ? A::to_u64(r[i]) : A::to_raw(r[i]);
 }
 
+template <class A, int LOGS, int LOGT, bool WHOLE, bool BNTT = false>
+__global__ void __launch_bounds__(TileGeo<LOGT>::NT, MulSmem<A, LOGT, false>::kMinB)
+k_row_polymul(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN, u32 B,
+              u32 limb0) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    row_polymul_body<A, LOGS, LOGT, WHOLE, BNTT, false>(a, b, c, tf, ti, logN, B, limb0, blockIdx.x, smem, nullptr);
+}
+
 // ---- persistent form of the fused row pass (two-pass transforms only) ---------------------------------------------------
 // One CTA per resident slot loops over tiles; the NEXT tile's operands are fetched by TMA bulk copies while the current
 // tile is computed, so no CTA ever waits for HBM at its start:
 //   a' -> the stash buffer (free once the pointwise product has read NTT(a)), landing during the inverse transform
 //   b' -> b's landing buffer (free once b has been read), landing during fwd(b), the product and the inverse transform
 // mbarrier phase `it & 1` of barA / barB belongs to loop trip `it`.
-__device__ __forceinline__ void mbar_init(u64* mbar) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
-}
-__device__ __forceinline__ void tma_tile_issue(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
-    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(u64* mbar, u32 parity) {
-    const u32 bar = smem_u32(mbar);
-    u32 done;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
-}
-
 template <class A, int LOGS, int LOGT>
 __global__ void __launch_bounds__(TileGeo<LOGT>::NT, MulSmem<A, LOGT, true>::kMinB)
 k_row_polymul_persist(const typename A::store* a, const typename A::store* b, typename A::store* c, const Tables tf, const Tables ti, u32 logN,
@@ -591,31 +627,33 @@ struct ColGeo {
 struct ColId { u64 base; u32 limb; };
 template <class W> constexpr int kColPad = sizeof(W) == 4 ? 1 : 2;   // padding of the column kernels' exchange (ntt_core.cuh, padk)
 template <int LOGC, int S>
-__device__ __forceinline__ ColId col_id(u32 B, u32 limb0) {
+__device__ __forceinline__ ColId col_id(u32 flat, u32 B, u32 limb0) {   // flat = polynomial * 2^LT + tile
     using Geo = ColGeo<LOGC, S>;
-    const u32 p = blockIdx.x >> Geo::LT, tile = blockIdx.x & ((1u << Geo::LT) - 1u);
+    const u32 p = flat >> Geo::LT, tile = flat & ((1u << Geo::LT) - 1u);
     return ColId{((u64)p << Geo::LOGN) + ((u64)tile << LOGC), limb0 + p / B};
 }
 
-template <class A, int LOGC, int S>
 #ifndef GFHE_COLB
 #define GFHE_COLB 4   // 64 registers: four resident CTAs per SM (measured: k_col_fwd -2.7 %, k_col_inv -8.7 % against 2 -> 3 resident)
 #endif
-__global__ void __launch_bounds__(256, GFHE_COLB)
-k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename A::store* in1, typename A::store* out1, const Tables tabs,
-          u32 B, u32 limb0) {
+// Exchange buffer (only when the pass has two windows) and the staged twiddles of a column tile.
+template <class A, int LOGC> struct ColSmem {
+    static constexpr u32 kExchWords = (LOGC < 8) ? padded_words(12) : 2;
+};
+
+template <class A, int LOGC, int S>
+__device__ __forceinline__ void col_fwd_body(const typename A::store* in0, typename A::store* out0, const Tables& tabs, u32 B, u32 limb0, u32 flat,
+                                             typename A::word* sm, typename A::tw_t* tws) {
     using Geo = ColGeo<LOGC, S>;
     typedef typename A::word W;
     typedef typename A::store St;
-    __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
+    typedef typename A::tw_t E;
     const u32 tid = threadIdx.x;
-    const ColId id = col_id<LOGC, S>(B, limb0);
-    const St* in = (blockIdx.y ? in1 : in0) + id.base;
-    St* out = (blockIdx.y ? out1 : out0) + id.base;
+    const ColId id = col_id<LOGC, S>(flat, B, limb0);
+    const St* in = in0 + id.base;
+    St* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    typedef typename A::tw_t E;
-    __shared__ E tws[256];
     W r[kElems];
     {
         const St* p = in + Geo::template toff<8>(tid);
@@ -642,28 +680,36 @@ k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename 
 
 template <class A, int LOGC, int S>
 __global__ void __launch_bounds__(256, GFHE_COLB)
-k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables tabs, u32 B, u32 limb0) {
+k_col_fwd(const typename A::store* in0, typename A::store* out0, const typename A::store* in1, typename A::store* out1, const Tables tabs,
+          u32 B, u32 limb0) {
+    __shared__ __align__(16) typename A::word sm[ColSmem<A, LOGC>::kExchWords];
+    __shared__ typename A::tw_t tws[256];
+    col_fwd_body<A, LOGC, S>(blockIdx.y ? in1 : in0, blockIdx.y ? out1 : out0, tabs, B, limb0, blockIdx.x, sm, tws);
+}
+
+// CG: the input is the output of row tiles of the same launch (pipelined kernels)
+template <class A, int LOGC, int S, bool CG = false>
+__device__ __forceinline__ void col_inv_body(const typename A::store* in0, typename A::store* out0, const Tables& tabs, u32 B, u32 limb0, u32 flat,
+                                             typename A::word* sm, typename A::tw_t* tws) {
     using Geo = ColGeo<LOGC, S>;
     typedef typename A::word W;
     typedef typename A::store St;
-    __shared__ __align__(16) W sm[Geo::TWO ? padded_words(12) : 2];
+    typedef typename A::tw_t E;
     const u32 tid = threadIdx.x;
-    const ColId id = col_id<LOGC, S>(B, limb0);
+    const ColId id = col_id<LOGC, S>(flat, B, limb0);
     const St* in = in0 + id.base;
     St* out = out0 + id.base;
     const LimbParams* __restrict__ Pg = tabs.params + id.limb;
     const LimbK<W> K = limb_consts<A>(Pg);
-    typedef typename A::tw_t E;
-    __shared__ E tws[256];
     W r[kElems];
     if constexpr (Geo::TWO) {
         const St* p = in + Geo::template toff<4>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<4>(i)], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, ld_res<CG>(p + Geo::template roff<4>(i)), tid * 77u + i);
     } else {
         const St* p = in + Geo::template toff<8>(tid);
 #pragma unroll
-        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, p[Geo::template roff<8>(i)], tid * 77u + i);
+        for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, ld_res<CG>(p + Geo::template roff<8>(i)), tid * 77u + i);
     }
     tws[tid] = __ldg(reinterpret_cast<const E*>(tabs.tw) + ((size_t)id.limb << Geo::LOGN) + tid);
     GFHE_SYNC();
@@ -679,6 +725,14 @@ k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables ta
     for (int i = 0; i < kElems; ++i) p[Geo::template roff<8>(i)] = A::to_u64(r[i]);
 }
 
+template <class A, int LOGC, int S>
+__global__ void __launch_bounds__(256, GFHE_COLB)
+k_col_inv(const typename A::store* in0, typename A::store* out0, const Tables tabs, u32 B, u32 limb0) {
+    __shared__ __align__(16) typename A::word sm[ColSmem<A, LOGC>::kExchWords];
+    __shared__ typename A::tw_t tws[256];
+    col_inv_body<A, LOGC, S>(in0, out0, tabs, B, limb0, blockIdx.x, sm, tws);
+}
+
 // ------------------------------------------------------------------------------------------------
 // host-side launchers, one set per arithmetic policy
 // ------------------------------------------------------------------------------------------------
@@ -690,6 +744,14 @@ static inline Tables inv_tables(const Plan& pl) { return Tables{pl.d_inv, pl.d_i
 
 // Stage split of a two-pass transform: S low (row) stages, log2 N - S <= 8 high (column) stages.
 static inline u32 row_stages(u32 logN) { return logN <= 16 ? 8u : 12u; }
+
+#include "ntt_pipe.inl"   // inside namespace gfhe
+
+// N > 4096: the pipelined single launch when the plan asks for it (GFHE_PIPE=1 at plan creation); default: one launch per pass
+#ifndef GFHE_PIPE_DEFAULT
+#define GFHE_PIPE_DEFAULT 0
+#endif
+static inline bool use_pipe(const Plan& pl) { return pl.pipe < 0 ? GFHE_PIPE_DEFAULT != 0 : pl.pipe == 1; }
 
 static inline unsigned tiles_of(const Plan& pl, u32 nl, u32 B) {
     const u32 logT = pl.logN < (u32)kMaxLogSlab ? pl.logN : (u32)kMaxLogSlab;
@@ -780,6 +842,7 @@ cudaError_t Launcher<A>::ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const typena
         }
         return cudaGetLastError();
     }
+    if (use_pipe(pl)) return pipe_ntt<A>(pl, false, limb0, nl, in, out, B, st);
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, in, out, nullptr, nullptr, B, nt, st)) return e;
     ProfScope ps(pl, K_ROW_FWD, st);
     if (row_stages(pl.logN) == 8) k_row_fwd<A, 8, 12><<<nt, 256, 0, st>>>(out, out, fwd_tables(pl), pl.logN, B, limb0);
@@ -799,6 +862,7 @@ cudaError_t Launcher<A>::ntt_inv(const Plan& pl, u32 limb0, u32 nl, const typena
         }
         return cudaGetLastError();
     }
+    if (use_pipe(pl)) return pipe_ntt<A>(pl, true, limb0, nl, in, out, B, st);
     {
         ProfScope ps(pl, K_ROW_INV, st);
         if (row_stages(pl.logN) == 8) k_row_inv<A, 8, 12, false><<<nt, 256, 0, st>>>(in, out, inv_tables(pl), pl.logN, B, limb0);
@@ -821,6 +885,7 @@ cudaError_t Launcher<A>::poly_mul(const Plan& pl, u32 limb0, u32 nl, const typen
         }
     }
     if (!ws) return cudaErrorInvalidValue;
+    if (use_pipe(pl)) return pipe_polymul<A, false>(pl, limb0, nl, a, b, c, ws, B, st);
     // high stages of a -> c (used as scratch), of b -> ws, in one launch (grid.y picks the operand)
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, b, ws, B, nt, st)) return e;
     cudaError_t e;
@@ -844,6 +909,7 @@ cudaError_t Launcher<A>::poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const t
             default: return cudaErrorInvalidValue;
         }
     }
+    if (use_pipe(pl)) return pipe_polymul<A, true>(pl, limb0, nl, a, b_ntt, c, nullptr, B, st);
     // high stages of a -> c (scratch), then the fused row pass against NTT(b), then the high inverse stages in place
     if (cudaError_t e = launch_col_fwd<A>(pl, limb0, a, c, nullptr, nullptr, B, nt, st)) return e;
     cudaError_t e = row_stages(pl.logN) == 8 ? launch_row_polymul<A, 8, 12, false, true>(pl, limb0, c, b_ntt, c, B, nt, st)

@@ -125,7 +125,7 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     pl->f64 = !pl->w32 && pl->max_bits <= 50 && logN != 0;
     if (const char* env = std::getenv("GFHE_FORCE_HARVEY")) if (env[0] == '1') pl->f64 = false;
     if (const char* env = std::getenv("GFHE_NO_F64")) if (env[0] == '1') pl->f64 = false;
-    if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
+    plan_read_env(pl);
     const bool f64 = pl->f64;
 
     std::vector<LimbParams> hp(L);
@@ -176,6 +176,29 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
     }
     *out = pl;
     return 0;
+}
+
+void plan_read_env(Plan* pl) {
+    if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
+    if (const char* env = std::getenv("GFHE_PIPE")) pl->pipe = env[0] == '1' ? 1 : 0;
+}
+
+cudaError_t pipe_sync_get(const Plan& pl, cudaStream_t st, size_t words, u32** out) {
+    std::lock_guard<std::mutex> lock(pl.sync_mu);
+    Plan::SyncBuf& sb = pl.sync_bufs[st];
+    if (sb.words < words) {
+        size_t cap = 1024;
+        while (cap < words) cap *= 2;
+        // the old buffer may still be read by a kernel in flight on st: cudaFree waits for the device
+        if (sb.d) cudaFree(sb.d);
+        sb.d = nullptr; sb.words = 0;
+        cudaError_t e = cudaMalloc(&sb.d, cap * sizeof(u32));
+        if (e != cudaSuccess) return e;
+        if ((e = cudaMemset(sb.d, 0, cap * sizeof(u32))) != cudaSuccess) return e;
+        sb.words = cap;
+    }
+    *out = sb.d;
+    return cudaSuccess;
 }
 
 // ---- plan image: save / load of the table cache ---------------------------------------------------
@@ -252,7 +275,7 @@ int plan_import(Plan** out, int device, const void* buf, size_t bytes) {
     Plan* pl = new Plan();
     pl->device = device; pl->logN = h.logN; pl->L = h.L; pl->max_bits = h.max_bits;
     pl->w32 = (h.flags & 1u) != 0; pl->f64 = (h.flags & 2u) != 0; pl->lazy = (h.flags & 4u) != 0;   // the policy the tables were built for
-    if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
+    plan_read_env(pl);
     pl->moduli.resize(h.L); std::memcpy(pl->moduli.data(), p, sizeof(u64) * h.L); p += sizeof(u64) * h.L;
     if (h.logN) { pl->psi.resize(h.L); std::memcpy(pl->psi.data(), p, sizeof(u64) * h.L); }
     p += sizeof(u64) * h.L;
@@ -333,6 +356,7 @@ int plan_destroy(Plan* p) {
         for (auto e : p->prof->pool) cudaEventDestroy(e);
         delete p->prof;
     }
+    for (auto& kv : p->sync_bufs) if (kv.second.d) cudaFree(kv.second.d);
     if (p->d_params) cudaFree(p->d_params);
     if (p->d_fwd) cudaFree(p->d_fwd);
     if (p->d_inv) cudaFree(p->d_inv);

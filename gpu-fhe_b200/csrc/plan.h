@@ -2,6 +2,8 @@
 // primitive 2N-th roots supplied by primitive.py and kept resident in HBM.
 #pragma once
 #include <cuda_runtime.h>
+#include <mutex>
+#include <unordered_map>
 #include <vector>
 #include "modarith.cuh"
 
@@ -9,7 +11,7 @@ namespace gfhe {
 
 // Optional per-kernel timing (gfhe_profile_enable): every launch is bracketed by cudaEvents on
 // its own stream, so bench.py can report each kernel's live duration and share of the step.
-enum KernelId { K_COL_FWD = 0, K_ROW_FWD, K_ROW_INV, K_COL_INV, K_ROW_POLYMUL, K_VEC, K_MAC, K_AUTO, K_COUNT };
+enum KernelId { K_COL_FWD = 0, K_ROW_FWD, K_ROW_INV, K_COL_INV, K_ROW_POLYMUL, K_VEC, K_MAC, K_AUTO, K_PIPE_FWD, K_PIPE_INV, K_PIPE_MUL, K_COUNT };
 struct Profiler {
     bool on = false;
     struct Rec { int kid; cudaEvent_t a, b; };
@@ -30,6 +32,7 @@ struct Plan {
     bool w32 = false;                  // every modulus is below 2^30: the Shoup32 kernels are used
     bool lazy = false;                 // every modulus is in [2^19, 2^60): the Lazy60 kernels are used
     int persist = -1;                  // fused row pass: -1 = per-policy default, 0 / 1 = GFHE_PERSIST at plan creation
+    int pipe = -1;                     // N > 4096: one pipelined launch with the intermediate in L2 (ntt_pipe.inl); -1 = default (on), 0 / 1 = GFHE_PIPE
     LimbParams* d_params = nullptr;    // [L]
     ulonglong2* d_fwd = nullptr;       // [L][N] {psi^brv(k), Shoup companion}; entry 0 unused
     ulonglong2* d_inv = nullptr;       // [L][N] {psi^-brv(k), Shoup companion}
@@ -37,6 +40,10 @@ struct Plan {
     ulonglong2* d_inv_t0 = nullptr;    // [L][N/512][15][32] same for d_inv (ntt_core.cuh, TwT0)
     std::vector<u64> moduli, psi;      // host copies (psi empty when logN == 0): what gfhe_plan_moduli / the plan image report
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
+    // synchronisation words of the pipelined kernels, one buffer per stream that launched one (left zeroed by every launch)
+    struct SyncBuf { u32* d = nullptr; size_t words = 0; };
+    mutable std::mutex sync_mu;
+    mutable std::unordered_map<cudaStream_t, SyncBuf> sync_bufs;
     Profiler* prof = nullptr;
 };
 
@@ -63,6 +70,9 @@ struct DeviceGuard {
 // plan.cu
 int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi);
 int plan_destroy(Plan* p);
+void plan_read_env(Plan* pl);   // GFHE_PERSIST / GFHE_PIPE
+// zeroed buffer of at least `words` 32-bit words for a pipelined launch on stream st (stream-ordered reuse)
+cudaError_t pipe_sync_get(const Plan& pl, cudaStream_t st, size_t words, u32** out);
 // Serialisable table cache: a plan image is the header + moduli + roots + the four device
 // tables exactly as they sit in HBM, so importing it is validation + four uploads -- no root search, no table generation.
 size_t plan_image_bytes(const Plan& pl);

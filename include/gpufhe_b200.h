@@ -186,6 +186,13 @@ int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, co
 #define GFHE_HOST_STATS_N           10
 int gfhe_host_stats(gfhe_plan_t plan, double* out, uint32_t n);
 
+/* Test hook (no GPU work): the ticket order of the pipelined kernels (ntt_pipe.inl) for `passes` passes with
+ * tiles_per_pass[k] tiles per polynomial, npoly polynomials and `resident` resident CTAs.  Writes (pass, polynomial,
+ * tile) triples for the first max_tickets tickets, the lag chosen (polynomials between a pass and its consumer), and
+ * returns the ticket count. */
+int gfhe_debug_pipe_schedule(uint32_t passes, const uint32_t* tiles_per_pass, uint32_t npoly, uint32_t resident,
+                             uint32_t* out, uint32_t max_tickets, uint32_t* lag);
+
 /* Measurement hook (bench.py): when enabled, every kernel launched through `plan` is bracketed
  * by cudaEvents on its stream.  gfhe_profile_read waits for them, writes up to max_kernels
  * (kernel name, summed milliseconds, launch count) triples and returns how many it wrote

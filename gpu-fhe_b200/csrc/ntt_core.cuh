@@ -310,6 +310,37 @@ __device__ __forceinline__ void sm_load(const W* sm, u32 tid, W (&r)[kElems]) {
     }
 }
 
+// ---- experiment (-DGFHE_EXP_SHFL): the north-star's "intra-warp butterflies with __shfl_sync" --------------------------
+// The exchange between the window at bit 4 and the window at bit 0 is a 16 x 16 transpose inside every group of 16
+// consecutive threads (register i of lane t <-> register t of lane i), so it CAN be done with warp shuffles instead of
+// shared memory: four butterfly steps, each swapping half of the registers with lane ^ s.  Per thread that is 32
+// exchanges x (2 selects + 1 shuffle + 2 selects) per 32-bit half -- ~8x the instructions of 16 stores + 16 loads, in
+// kernels that are bound by instruction issue.  Kept as a measured A/B, not as the product path.
+template <class W>
+__device__ __forceinline__ W shfl_xor_word(W v, int s) {
+    if constexpr (sizeof(W) == 8) {
+        const unsigned long long b = sizeof(W) == 8 ? *reinterpret_cast<unsigned long long*>(&v) : 0ull;
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, b, s);
+        return *reinterpret_cast<const W*>(&o);
+    } else {
+        return __shfl_xor_sync(0xffffffffu, v, s);
+    }
+}
+template <class W>
+__device__ __forceinline__ void shfl_transpose16(W (&r)[kElems], u32 tid) {
+#pragma unroll
+    for (int s = 1; s < 16; s <<= 1) {
+        const bool up = (tid & s) != 0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (i & s) continue;
+            const W send = up ? r[i] : r[i | s];
+            const W recv = shfl_xor_word(send, s);
+            if (up) r[i] = recv; else r[i | s] = recv;
+        }
+    }
+}
+
 // Round schedule of a 2^LOGS contiguous slab: round k covers slab bits [p0(k), top(k)).
 template <int LOGS>
 struct Sched {
@@ -350,17 +381,27 @@ __device__ __forceinline__ void slab_fwd(typename A::word (&r)[kElems], typename
     }
     if constexpr (S::NR > 1) {
         constexpr int PP = S::p0(0), P0 = S::p0(1);
+#ifdef GFHE_EXP_SHFL
+        if constexpr (PP == 4 && P0 == 0) shfl_transpose16(r, tid); else
+#endif
+        {
         sm_store<PP>(sm, tid, r);
         GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
+        }
         fwd_round<A, S::top(1) - 1 - P0, 0, decltype(round_tw<P0>(T, off, tid)), fwd_bound(ENTRY, LOGS - S::top(1))>(r, round_tw<P0>(T, off, tid), C, nq);
     }
     if constexpr (S::NR > 2) {
         constexpr int PP = S::p0(1), P0 = S::p0(2);
+#ifdef GFHE_EXP_SHFL
+        if constexpr (PP == 4 && P0 == 0) shfl_transpose16(r, tid); else
+#endif
+        {
         // no barrier needed: every thread overwrites exactly the words it read in the previous exchange
         sm_store<PP>(sm, tid, r);
         GFHE_SYNC();
         sm_load<P0>(sm, tid, r);
+        }
         fwd_round<A, S::top(2) - 1 - P0, 0, decltype(round_tw<P0>(T, off, tid)), fwd_bound(ENTRY, LOGS - S::top(2))>(r, round_tw<P0>(T, off, tid), C, nq);
     }
 }

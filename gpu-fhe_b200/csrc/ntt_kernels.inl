@@ -234,6 +234,45 @@ __device__ __forceinline__ void copy_in_padded(u64* sm, const u64* in, u32 tid) 
     }
 }
 
+// ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+// one thread: arm the barrier with the byte count and start the copy
+// Shared-memory layout of the fused poly-mul kernels, in bytes: exchange buffer | stash of NTT(a) (the persistent form
+// also lands the next a tile there, linear, in storage words) | b's landing buffer | two mbarriers.
+template <class A, int LOGT, bool PERSIST>
+struct MulSmem {
+    typedef typename A::word W;
+    typedef typename A::store S;
+    static constexpr u32 kExch = ((u32)sizeof(W) * padded_words(LOGT) + 15u) & ~15u;
+    static constexpr u32 kTile = (u32)sizeof(S) << LOGT;
+    static constexpr u32 kStash = (PERSIST && kTile > kExch) ? kTile : kExch;
+    static constexpr u32 kOff1 = kExch, kOffB = kExch + kStash, kOffBar = kOffB + kTile, kBytes = kOffBar + 16;
+    static_assert(kOff1 % 16 == 0 && kOffB % 16 == 0 && kOffBar % 8 == 0, "TMA destinations are 16-byte aligned");
+    // resident CTAs per SM the kernel is compiled for: three when shared memory (227 KB) and 80 registers allow
+    static constexpr int kFit = (int)((227u * 1024u) / (kBytes + 1024u));
+    static constexpr int kMinB = LOGT == 12 ? ((sizeof(W) == 4 && kFit >= 3) ? (kFit < GFHE_MINB32 ? kFit : GFHE_MINB32) : GFHE_MINB) : 1;
+};
+
+__device__ __forceinline__ void tma_tile_load(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
+    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
+}
+// every thread: wait for phase 0 of the barrier (the copy has landed and is visible)
+__device__ __forceinline__ void tma_tile_wait(u64* mbar) {
+    const u32 bar = smem_u32(mbar);
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "GFHE_TMA_WAIT:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+        "@!p bra GFHE_TMA_WAIT;\n\t"
+        "}\n" ::"r"(bar) : "memory");
+}
+
 // Forward: the LOGS low stages + full reduction to [0, q).  Always the last pass of a forward NTT.
 // The tile bodies are device functions of the tile index: the stand-alone kernels call them with blockIdx.x, the pipelined
 // kernels at the end of this file with the tile their ticket names.
@@ -249,6 +288,19 @@ __device__ __forceinline__ void row_fwd_body(const typename A::store* in, typena
     const auto T = limb_tables<A>(tabs, s.limb, logN);
     W r[kElems];
     constexpr int P0 = Sched<LOGS>::p0(0);
+#ifdef GFHE_EXP_TMAROW
+    // experiment ("TMA staging of every sub-transform"): the tile arrives by ONE cp.async.bulk into the
+    // (not yet used) exchange buffer instead of 16 LDG per thread, and the registers are filled from shared memory
+    if constexpr (LOGT == 12 && sizeof(S) == sizeof(W) && !A::kFloat) {
+        __shared__ __align__(8) u64 exp_mbar;
+        if (tid == 0) tma_tile_load(sm, in + s.g0, (u32)sizeof(S) << LOGT, &exp_mbar);
+        __syncthreads();
+        tma_tile_wait(&exp_mbar);
+#pragma unroll
+        for (int i = 0; i < kElems; ++i) r[i] = A::from_raw(reinterpret_cast<const S*>(sm)[elem_index<P0>(tid, 0) + (i << P0)]);
+        __syncthreads();   // the exchange of the first round overwrites the landing buffer
+    } else
+#endif
     if (A::kFloat && logN > (u32)LOGT) {   // second pass of a large transform: the column pass left raw words (they differ from canonical ones for the FP64 policy only)
 #pragma unroll
         for (int i = 0; i < kElems; ++i) r[i] = GFHE_GLD(A::from_raw, ld_res<CG>(in + s.g0 + elem_index<P0>(tid, 0) + (i << P0)), tid * 77u + i);
@@ -318,45 +370,6 @@ k_row_inv(const typename A::store* in, typename A::store* out, const Tables tabs
     __shared__ __align__(16) W sm[padded_words(LOGT)];
     prefetch_row_tile<LOGT, RowPf<A>::kInv>(in, threadIdx.x);
     row_inv_body<A, LOGS, LOGT, WHOLE>(in, out, tabs, logN, B, limb0, blockIdx.x, sm);
-}
-
-// ---- TMA bulk copy (cp.async.bulk) of one contiguous tile into shared memory, completion on an mbarrier ----
-__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
-// one thread: arm the barrier with the byte count and start the copy
-// Shared-memory layout of the fused poly-mul kernels, in bytes: exchange buffer | stash of NTT(a) (the persistent form
-// also lands the next a tile there, linear, in storage words) | b's landing buffer | two mbarriers.
-template <class A, int LOGT, bool PERSIST>
-struct MulSmem {
-    typedef typename A::word W;
-    typedef typename A::store S;
-    static constexpr u32 kExch = ((u32)sizeof(W) * padded_words(LOGT) + 15u) & ~15u;
-    static constexpr u32 kTile = (u32)sizeof(S) << LOGT;
-    static constexpr u32 kStash = (PERSIST && kTile > kExch) ? kTile : kExch;
-    static constexpr u32 kOff1 = kExch, kOffB = kExch + kStash, kOffBar = kOffB + kTile, kBytes = kOffBar + 16;
-    static_assert(kOff1 % 16 == 0 && kOffB % 16 == 0 && kOffBar % 8 == 0, "TMA destinations are 16-byte aligned");
-    // resident CTAs per SM the kernel is compiled for: three when shared memory (227 KB) and 80 registers allow
-    static constexpr int kFit = (int)((227u * 1024u) / (kBytes + 1024u));
-    static constexpr int kMinB = LOGT == 12 ? ((sizeof(W) == 4 && kFit >= 3) ? (kFit < GFHE_MINB32 ? kFit : GFHE_MINB32) : GFHE_MINB) : 1;
-};
-
-__device__ __forceinline__ void tma_tile_load(void* dst_smem, const void* src_gmem, u32 bytes, u64* mbar) {
-    const u32 bar = smem_u32(mbar), dst = smem_u32(dst_smem);
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
-}
-// every thread: wait for phase 0 of the barrier (the copy has landed and is visible)
-__device__ __forceinline__ void tma_tile_wait(u64* mbar) {
-    const u32 bar = smem_u32(mbar);
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "GFHE_TMA_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
-        "@!p bra GFHE_TMA_WAIT;\n\t"
-        "}\n" ::"r"(bar) : "memory");
 }
 
 // mbarrier pieces used by the pipelined and persistent kernels: init once, then one phase per tile

@@ -43,6 +43,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version line to stdout), so file
+# descriptor 1 is pointed at stderr for the life of the process and the line goes to a private copy of the real stdout.
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -202,7 +221,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": "limb-poly-mul/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 class Ctx:
@@ -576,6 +595,13 @@ def run_b200(args, rank, world, local_rank):
     pg_s, pg_hs = e2e_leg(pg_a, pg_b, pg_c, pg_steps)
     ok = ok and (np.array_equal(pg_c[0, 0], want_local[0, 0]) if rank == 0 else True)
     assert pg_hs["staged"] == 1.0 and hs["staged"] == 0.0
+    # ... and the same arrays handed to the driver as they are (cudaMemcpyAsync from pageable memory: the driver stages them
+    # itself, one thread, and the three streams serialise) -- what the call did before the staging ring existed
+    os.environ["GFHE_HOST_STAGING"] = "0"
+    try:
+        raw_s, _ = e2e_leg(pg_a, pg_b, pg_c, max(2, pg_steps // 2))
+    finally:
+        del os.environ["GFHE_HOST_STAGING"]
     # host memory copy rate with every rank copying at once (what staging and the DMA engines share)
     cx.barrier()
     t0 = time.perf_counter()
@@ -662,7 +688,9 @@ def run_b200(args, rank, world, local_rank):
                 "copies": e2e_host},
         "e2e_pageable": {"value": UNITS_TOTAL / pg_s, "unit": "limb-poly-mul/s", "steps": pg_steps, "ms_per_step": pg_s * 1e3,
                          "stage_in_ms": pg_hs["stage_in_ms"], "stage_out_ms": pg_hs["stage_out_ms"],
-                         "api": "same call with plain (pageable) numpy arrays: staged through the library's pinned ring by host threads"},
+                         "unstaged_ms_per_step": raw_s * 1e3,
+                         "api": "same call with plain (pageable) numpy arrays: staged through the library's pinned ring by host threads "
+                                "(unstaged = GFHE_HOST_STAGING=0, the driver's own pageable path)"},
         "host_copy": host_copy,
         "gather": gather,
         "extra": {"weak": weak, "configs": configs, "config5_sweep": sweep,
@@ -675,7 +703,7 @@ def run_b200(args, rank, world, local_rank):
         "clocks": clocks.summary(),
         "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -689,6 +717,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="skip the config-5 N=2^17 grid (49 points)")
     args = ap.parse_args()
+    claim_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -2,6 +2,7 @@
 // host-buffer entry points that pipeline H2D -> kernels -> D2H over limb groups.
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <chrono>
 #include <cstring>
 #include <thread>
@@ -444,7 +445,9 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     // pageable operands are staged through pinned buffers (GFHE_HOST_STAGING=0 hands them to the driver as they are)
     bool staged = !(host_ptr_is_pinned(h_a) && host_ptr_is_pinned(h_c) && (op != 2 || host_ptr_is_pinned(h_b)));
     if (const char* env = std::getenv("GFHE_HOST_STAGING")) if (env[0] == '0') staged = false;
-    unsigned nthr = 4;
+    unsigned nthr = std::thread::hardware_concurrency() / 2;   // staging threads: half the cores, 2..8
+    if (nthr < 2) nthr = 2;
+    if (nthr > 8) nthr = 8;
     if (const char* env = std::getenv("GFHE_HOST_COPY_THREADS")) { const long v = std::atol(env); if (v >= 1 && v <= 64) nthr = (unsigned)v; }
     const size_t limb_elems = (size_t)batch << pl->logN;
     // group schedule: full groups, then a halving tail (gl/2, gl/4, ..., 1) so that what is left after the last H2D
@@ -460,15 +463,29 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     if (e) return (int)e;
     constexpr int kS = HostPipe::kSlots;
     double stage_in_ms = 0, stage_out_ms = 0;
-    auto drain = [&](size_t it) -> cudaError_t {   // staged mode: group `it`'s result from its pinned slot to the caller's array
-        const int slot = (int)(it % kS);
-        if (cudaError_t de = cudaEventSynchronize(hp->out_done[slot])) return de;
-        const double t0 = now_ms();
-        par_memcpy(h_c + limb_elems * first[it], hp->pin[slot][2], limb_bytes * groups[it], nthr);
-        stage_out_ms += now_ms() - t0;
-        return cudaSuccess;
-    };
-    size_t issued = 0, drained = 0;
+    // staged mode: a drain thread copies finished groups out of their pinned slots (in order) while this thread stages
+    // the next inputs in; `issued` / `drained` are the hand-shake (a slot is reused only after its group was drained)
+    std::atomic<size_t> issued{0}, drained{0};
+    std::atomic<int> drain_err{0};
+    std::atomic<bool> abort_drain{false};
+    const unsigned in_thr = nthr, out_thr = nthr > 2 ? nthr / 2 : 1;
+    std::thread drainer;
+    if (staged)
+        drainer = std::thread([&]() {
+            cudaSetDevice(pl->device);
+            for (size_t g2 = 0; g2 < groups.size(); ++g2) {
+                while (issued.load(std::memory_order_acquire) <= g2) {
+                    if (abort_drain.load(std::memory_order_acquire)) return;
+                    std::this_thread::yield();
+                }
+                const int slot = (int)(g2 % kS);
+                if (cudaError_t de = cudaEventSynchronize(hp->out_done[slot])) { drain_err.store((int)de); return; }
+                const double t0 = now_ms();
+                par_memcpy(h_c + limb_elems * first[g2], hp->pin[slot][2], limb_bytes * groups[g2], out_thr);
+                stage_out_ms += now_ms() - t0;
+                drained.store(g2 + 1, std::memory_order_release);
+            }
+        });
     auto body = [&]() -> cudaError_t {
         for (size_t it = 0; it < groups.size(); ++it) {
             const int slot = (int)(it % kS);
@@ -478,10 +495,14 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
             const u64 *src_a = h_a + off, *src_b = h_b ? h_b + off : nullptr;
             u64* dst_c = h_c + off;
             if (staged) {
-                if (it >= (size_t)kS) { if ((e = drain(it - kS))) return e; drained = it - kS + 1; }   // frees the slot's three staging buffers
+                if (it >= (size_t)kS)   // the slot's three staging buffers are free once its previous group was drained
+                    while (drained.load(std::memory_order_acquire) < it - kS + 1) {
+                        if (drain_err.load()) return (cudaError_t)drain_err.load();
+                        std::this_thread::yield();
+                    }
                 const double t0 = now_ms();
-                par_memcpy(hp->pin[slot][0], src_a, bytes, nthr);
-                if (op == 2) par_memcpy(hp->pin[slot][1], src_b, bytes, nthr);
+                par_memcpy(hp->pin[slot][0], src_a, bytes, in_thr);
+                if (op == 2) par_memcpy(hp->pin[slot][1], src_b, bytes, in_thr);
                 stage_in_ms += now_ms() - t0;
                 src_a = hp->pin[slot][0]; src_b = hp->pin[slot][1]; dst_c = hp->pin[slot][2];
             }
@@ -508,18 +529,22 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
             if ((e = cudaMemcpyAsync(dst_c, dc, bytes, cudaMemcpyDeviceToHost, hp->s_out))) return e;
             if ((e = cudaEventRecord(tv[5], hp->s_out))) return e;
             if ((e = cudaEventRecord(hp->out_done[slot], hp->s_out))) return e;
-            issued = it + 1;
+            issued.store(it + 1, std::memory_order_release);
         }
-        if (staged) for (; drained < groups.size(); ++drained) if ((e = drain(drained))) return e;
         return cudaSuccess;
     };
     e = body();
+    if (staged) {
+        if (e != cudaSuccess) abort_drain.store(true, std::memory_order_release);   // groups that were never issued will not arrive
+        drainer.join();
+        if (e == cudaSuccess && drain_err.load()) e = (cudaError_t)drain_err.load();
+    }
     // success or not, nothing of this call may still be in flight on the caller's buffers when it returns
     const cudaError_t e1 = cudaStreamSynchronize(hp->s_out), e2 = cudaStreamSynchronize(hp->s_run), e3 = cudaStreamSynchronize(hp->s_in);
     if (e == cudaSuccess) e = e1 ? e1 : (e2 ? e2 : e3);
     if (e) return (int)e;
     double busy[3] = {0, 0, 0};
-    for (size_t it = 0; it < issued; ++it)
+    for (size_t it = 0; it < issued.load(); ++it)
         for (int k = 0; k < 3; ++k) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, hp->tev[6 * it + 2 * k], hp->tev[6 * it + 2 * k + 1]) == cudaSuccess) busy[k] += ms;

@@ -37,7 +37,12 @@ __device__ __forceinline__ void pipe_next(const PipeSched& sc, u32* sync, volati
     if (pass > 0) {
         const u32* flag = sync + 2 + (size_t)(pass - 1) * sc.npoly + poly;
         const u32 need = sc.n[pass - 1];
-        while (ld_acquire_gpu(flag) < need) __nanosleep(64);
+        // bounded: producers are running CTAs, so the wait is microseconds; a schedule bug must fail the launch, not hang the GPU
+        u32 polls = 0;
+        while (ld_acquire_gpu(flag) < need) {
+            __nanosleep(64);
+            if (++polls > (1u << 23)) asm volatile("trap;");
+        }
         asm volatile("fence.proxy.async;" ::: "memory");   // the producers used generic stores; this thread may read them by TMA next
     }
 }

@@ -165,7 +165,7 @@ int gfhe_automorphism(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint
 /* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan.  Limb groups are streamed
  * H2D -> kernels -> D2H on separate streams so copies overlap compute.  Pinned arrays are copied from / to in place;
  * pageable arrays (plain numpy / malloc memory) are staged through an internal ring of pinned buffers by a few host
- * threads (GFHE_HOST_COPY_THREADS, default 4), so the three streams still overlap.  Synchronous: nothing is in flight
+ * threads (GFHE_HOST_COPY_THREADS, default half the cores, at most 8) while a drain thread copies finished groups out, so the three streams still overlap.  Synchronous: nothing is in flight
  * on the caller's buffers when the call returns, on error paths included. */
 int gfhe_ntt_host(gfhe_plan_t plan, int inverse, uint32_t batch, const uint64_t* h_in, uint64_t* h_out);
 int gfhe_poly_mul_host(gfhe_plan_t plan, uint32_t batch, const uint64_t* h_a, const uint64_t* h_b, uint64_t* h_c);

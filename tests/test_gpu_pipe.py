@@ -51,7 +51,7 @@ def test_pipelined_kernels_match_oracle(cuda_device, pipe_on, monkeypatch, bits,
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     N = 1 << logn
-    moduli = P.ntt_primes(bits, L)
+    moduli = P.ntt_primes(bits, L, N=max(N, 1 << 17))       # q = 1 mod 2N
     a, b = rand_lbn(logn + bits, moduli, B, N), rand_lbn(logn + bits + 1, moduli, B, N)
     R = cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli])
     ta, tb = dev(a, cuda_device, packed), dev(b, cuda_device, packed)

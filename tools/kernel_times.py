@@ -28,4 +28,4 @@ for name, f in (("polymul", pm), ("ntt", nt), ("intt", it)):
     lib.gfhe_profile_enable(plan.handle, 1); [f() for _ in range(20)]
     names = (ctypes.c_char_p * 8)(); tot = (ctypes.c_double * 8)(); cnt = (ctypes.c_uint64 * 8)()
     nk = lib.gfhe_profile_read(plan.handle, 8, names, tot, cnt); lib.gfhe_profile_enable(plan.handle, 0)
-    print(os.environ.get("TAG", "base"), name, "step %.4f ms |" % total, "  ".join("%s %.4f" % (names[i].decode(), tot[i] / cnt[i]) for i in range(nk)), flush=True)
+    print(os.environ.get("TAG", "base"), "bits=%d%s pipe=%s" % (bits, " packed" if PACKED else "", os.environ.get("GFHE_PIPE", "-")), name, "step %.4f ms |" % total, "  ".join("%s %.4f" % (names[i].decode(), tot[i] / cnt[i]) for i in range(nk)), flush=True)

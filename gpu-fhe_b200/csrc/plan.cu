@@ -181,6 +181,7 @@ int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, cons
 void plan_read_env(Plan* pl) {
     if (const char* env = std::getenv("GFHE_PERSIST")) pl->persist = env[0] == '1' ? 1 : 0;
     if (const char* env = std::getenv("GFHE_PIPE")) pl->pipe = env[0] == '1' ? 1 : 0;
+    if (const char* env = std::getenv("GFHE_SPLIT")) pl->split = env[0] == '1' ? 1 : 0;
 }
 
 cudaError_t pipe_sync_get(const Plan& pl, cudaStream_t st, size_t words, u32** out) {
@@ -305,40 +306,103 @@ extern template struct Launcher<Shoup32>;
 extern template struct Launcher<Fp50>;
 extern template struct Launcher<Shoup32P>;
 
-cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+// one policy's launcher for a limb range, single stream
+static cudaError_t do_ntt(const Plan& pl, bool inv, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    if (inv) {
+        if (pl.w32) return Launcher<Shoup32>::ntt_inv(pl, limb0, nl, in, out, B, st);
+        if (pl.f64) return Launcher<Fp50>::ntt_inv(pl, limb0, nl, in, out, B, st);
+        return pl.lazy ? Launcher<Lazy60>::ntt_inv(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_inv(pl, limb0, nl, in, out, B, st);
+    }
     if (pl.w32) return Launcher<Shoup32>::ntt_fwd(pl, limb0, nl, in, out, B, st);
     if (pl.f64) return Launcher<Fp50>::ntt_fwd(pl, limb0, nl, in, out, B, st);
     return pl.lazy ? Launcher<Lazy60>::ntt_fwd(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_fwd(pl, limb0, nl, in, out, B, st);
 }
-cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    if (pl.w32) return Launcher<Shoup32>::ntt_inv(pl, limb0, nl, in, out, B, st);
-    if (pl.f64) return Launcher<Fp50>::ntt_inv(pl, limb0, nl, in, out, B, st);
-    return pl.lazy ? Launcher<Lazy60>::ntt_inv(pl, limb0, nl, in, out, B, st) : Launcher<Harvey>::ntt_inv(pl, limb0, nl, in, out, B, st);
-}
-cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
+static cudaError_t do_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
     if (pl.f64) return Launcher<Fp50>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st)
                    : Launcher<Harvey>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st);
 }
-cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
+static cudaError_t do_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
     if (pl.w32) return Launcher<Shoup32>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
     if (pl.f64) return Launcher<Fp50>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
     return pl.lazy ? Launcher<Lazy60>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st)
                    : Launcher<Harvey>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st);
 }
+
+// ---- two-stream split of small jobs ---------------------------------------------------------------
+// A two-pass transform is one grid per pass and the product three; with a few hundred to a few thousand tiles (a limb shard
+// of config 4 on 8 GPUs is 1024 tiles per grid on 296-592 resident CTAs) the last, partly filled wave of every grid leaves
+// SMs idle.  Such a job is cut into two limb halves that run on the caller's stream and on a stream of the plan's own,
+// forked and joined with events, so one half's tails are filled by the other half's kernels.  Measured on the 8-GPU shard
+// [4,16,65536] (profiles/r02_run7_chunk_probe_shard.txt): poly-mul 0.1402 -> 0.1317 ms, NTT 0.0515 -> 0.0472 ms; at the
+// full [32,16,65536] the grids are 14-28 waves deep and the split gains nothing, so it is applied to small jobs only.
+// GFHE_SPLIT=0 / 1 at plan creation: never / whenever there are two limbs.
+static bool want_split(const Plan& pl, u32 nl, u32 B) {
+    if (pl.split == 0 || pl.logN <= 12 || nl < 2 || pl.pipe == 1) return false;
+    if (pl.split == 1) return true;
+    const u64 tiles = ((u64)nl * B) << (pl.logN - 12);
+    return tiles >= 512 && tiles <= 4096;
+}
+template <class F>   // run(limb0, nl, offset of the range in limb-rows, stream)
+static cudaError_t split_run(const Plan& pl, u32 limb0, u32 nl, u32 B, cudaStream_t st, F run) {
+    if (!want_split(pl, nl, B)) return run(limb0, nl, 0u, st);
+    std::lock_guard<std::mutex> lock(pl.sync_mu);   // the fork / join events are the plan's: one enqueue sequence at a time
+    cudaError_t e;
+    if (!pl.aux_stream) {
+        if ((e = cudaStreamCreateWithFlags(&pl.aux_stream, cudaStreamNonBlocking))) return e;
+        if ((e = cudaEventCreateWithFlags(&pl.ev_fork, cudaEventDisableTiming))) return e;
+        if ((e = cudaEventCreateWithFlags(&pl.ev_join, cudaEventDisableTiming))) return e;
+    }
+    const u32 h = nl / 2;
+    if ((e = cudaEventRecord(pl.ev_fork, st))) return e;
+    if ((e = cudaStreamWaitEvent(pl.aux_stream, pl.ev_fork, 0))) return e;
+    if ((e = run(limb0, h, 0u, st))) return e;
+    e = run(limb0 + h, nl - h, h, pl.aux_stream);
+    // join even after a failed launch: the caller's stream must not run ahead of what was enqueued on the other one
+    cudaError_t e2 = cudaEventRecord(pl.ev_join, pl.aux_stream);
+    if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(st, pl.ev_join, 0);
+    return e ? e : e2;
+}
+
+cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_ntt(pl, false, l0, n, in + off * row, out + off * row, B, s); });
+}
+cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_ntt(pl, true, l0, n, in + off * row, out + off * row, B, s); });
+}
+cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) {
+        return do_poly_mul(pl, l0, n, a + off * row, b + off * row, c + off * row, ws ? ws + off * row : nullptr, B, s); });
+}
+cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_poly_mul_pre(pl, l0, n, a + off * row, b_ntt + off * row, c + off * row, B, s); });
+}
 // packed layout: only plans on the 32-bit policy have it (every modulus below 2^30)
 cudaError_t launch_ntt_fwd_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
-    return pl.w32 ? Launcher<Shoup32P>::ntt_fwd(pl, limb0, nl, in, out, B, st) : cudaErrorNotSupported;
+    if (!pl.w32) return cudaErrorNotSupported;
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_fwd(pl, l0, n, in + off * row, out + off * row, B, s); });
 }
 cudaError_t launch_ntt_inv_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
-    return pl.w32 ? Launcher<Shoup32P>::ntt_inv(pl, limb0, nl, in, out, B, st) : cudaErrorNotSupported;
+    if (!pl.w32) return cudaErrorNotSupported;
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_inv(pl, l0, n, in + off * row, out + off * row, B, s); });
 }
 cudaError_t launch_poly_mul_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b, u32* c, u32* ws, u32 B, cudaStream_t st) {
-    return pl.w32 ? Launcher<Shoup32P>::poly_mul(pl, limb0, nl, a, b, c, ws, B, st) : cudaErrorNotSupported;
+    if (!pl.w32) return cudaErrorNotSupported;
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) {
+        return Launcher<Shoup32P>::poly_mul(pl, l0, n, a + off * row, b + off * row, c + off * row, ws ? ws + off * row : nullptr, B, s); });
 }
 cudaError_t launch_poly_mul_pre_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b_ntt, u32* c, u32 B, cudaStream_t st) {
-    return pl.w32 ? Launcher<Shoup32P>::poly_mul_pre(pl, limb0, nl, a, b_ntt, c, B, st) : cudaErrorNotSupported;
+    if (!pl.w32) return cudaErrorNotSupported;
+    const size_t row = (size_t)B << pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::poly_mul_pre(pl, l0, n, a + off * row, b_ntt + off * row, c + off * row, B, s); });
 }
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
     if (pl.logN <= 12) return 0;
@@ -357,6 +421,9 @@ int plan_destroy(Plan* p) {
         delete p->prof;
     }
     for (auto& kv : p->sync_bufs) if (kv.second.d) cudaFree(kv.second.d);
+    if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+    if (p->ev_join) cudaEventDestroy(p->ev_join);
+    if (p->aux_stream) cudaStreamDestroy(p->aux_stream);
     if (p->d_params) cudaFree(p->d_params);
     if (p->d_fwd) cudaFree(p->d_fwd);
     if (p->d_inv) cudaFree(p->d_inv);

@@ -39,6 +39,9 @@ struct Plan {
     ulonglong2* d_fwd_t0 = nullptr;    // [L][N/512][15][32] warp-tiled copy of d_fwd for the window at bit 0
     ulonglong2* d_inv_t0 = nullptr;    // [L][N/512][15][32] same for d_inv (ntt_core.cuh, TwT0)
     std::vector<u64> moduli, psi;      // host copies (psi empty when logN == 0): what gfhe_plan_moduli / the plan image report
+    int split = -1;                    // two-stream split of small jobs (plan.cu, split_run): -1 = by size, 0 / 1 = GFHE_SPLIT
+    mutable cudaStream_t aux_stream = nullptr;      // second stream of split_run, with its fork / join events
+    mutable cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     void* host_pipe = nullptr;         // staging buffers/streams of the *_host entry points (capi.cu)
     // synchronisation words of the pipelined kernels, one buffer per stream that launched one (left zeroed by every launch)
     struct SyncBuf { u32* d = nullptr; size_t words = 0; };
@@ -70,7 +73,7 @@ struct DeviceGuard {
 // plan.cu
 int plan_create(Plan** out, int device, u32 logN, u32 L, const u64* moduli, const u64* psi);
 int plan_destroy(Plan* p);
-void plan_read_env(Plan* pl);   // GFHE_PERSIST / GFHE_PIPE
+void plan_read_env(Plan* pl);   // GFHE_PERSIST / GFHE_PIPE / GFHE_SPLIT
 // zeroed buffer of at least `words` 32-bit words for a pipelined launch on stream st (stream-ordered reuse)
 cudaError_t pipe_sync_get(const Plan& pl, cudaStream_t st, size_t words, u32** out);
 // Serialisable table cache: a plan image is the header + moduli + roots + the four device

@@ -4,6 +4,12 @@ Every limb-polynomial is independent (twiddles depend only on (N, q_limb)), so t
 no cross-GPU traffic.  Limbs are split first (each rank then holds only its limbs' tables), the
 batch only when L < world.  The one collective is the final all-gather of result limbs back to
 every caller's device (NCCL over NVLink; gloo in the CPU tests).
+
+Two limb-to-rank maps.  Block (default): rank i holds limbs [i*L/g, (i+1)*L/g) -- one all-gather of
+the whole shard lands in natural limb order.  Cyclic: rank i holds limbs i, i+g, i+2g, ... -- then
+the k-th local limbs of all ranks are the CONTIGUOUS slab [k*g, (k+1)*g) of the result, so the
+gather can be issued limb by limb, each one overlapping the next limb's kernels
+(all_gather_limb_async); with the block map a per-limb gather would land strided.
 """
 from __future__ import annotations
 
@@ -19,19 +25,27 @@ class Shard:
     world: int
     g_l: int          # ranks along the limb axis
     g_b: int          # ranks along the batch axis
-    limbs: Tuple[int, int]    # [lo, hi)
+    limbs: Tuple[int, int]    # block map: [lo, hi);  cyclic map: (first limb, L) -- use limb_ids
     batch: Tuple[int, int]    # [lo, hi)
+    cyclic: bool = False
+
+    @property
+    def limb_ids(self) -> Tuple[int, ...]:
+        """Global indices of the limbs this rank holds, in local order."""
+        if self.cyclic:
+            return tuple(range(self.limbs[0], self.limbs[1], self.g_l))
+        return tuple(range(self.limbs[0], self.limbs[1]))
 
     @property
     def num_limbs(self) -> int:
-        return self.limbs[1] - self.limbs[0]
+        return len(self.limb_ids)
 
     @property
     def num_batch(self) -> int:
         return self.batch[1] - self.batch[0]
 
 
-def partition(L: int, B: int, world: int, rank: int) -> Shard:
+def partition(L: int, B: int, world: int, rank: int, cyclic: bool = False) -> Shard:
     """g_l = largest divisor of `world` that is <= L and divides L evenly when possible."""
     if world < 1 or not 0 <= rank < world:
         raise ValueError("bad rank/world")
@@ -44,11 +58,15 @@ def partition(L: int, B: int, world: int, rank: int) -> Shard:
         raise ValueError("cannot split L=%d, B=%d evenly over %d ranks (g_l=%d, g_b=%d)" % (L, B, world, g_l, g_b))
     i, j = divmod(rank, g_b)
     lpr, bpr = L // g_l, B // g_b
+    if cyclic:
+        return Shard(rank, world, g_l, g_b, (i, L), (j * bpr, (j + 1) * bpr), True)
     return Shard(rank, world, g_l, g_b, (i * lpr, (i + 1) * lpr), (j * bpr, (j + 1) * bpr))
 
 
 def take(x: torch.Tensor, sh: Shard) -> torch.Tensor:
     """The rank's block of a full [L, B, N] tensor (contiguous copy)."""
+    if sh.cyclic:
+        return x[sh.limbs[0]:sh.limbs[1]:sh.g_l, sh.batch[0]:sh.batch[1]].contiguous()
     return x[sh.limbs[0]:sh.limbs[1], sh.batch[0]:sh.batch[1]].contiguous()
 
 
@@ -56,12 +74,31 @@ def all_gather_limbs(local: torch.Tensor, sh: Shard, group=None) -> torch.Tensor
     """All-gather the per-rank [L/g_l, B/g_b, N] blocks into the full [L, B, N] on every rank."""
     import torch.distributed as dist
     l, b, n = local.shape
+    if sh.cyclic:                      # limb by limb, each into its contiguous slab of the result
+        full = torch.empty((sh.g_l * l, sh.g_b * b, n), dtype=local.dtype, device=local.device)
+        works = [all_gather_limb_async(local[k], full, k, sh, group) for k in range(l)]
+        for w in works:
+            w.wait()
+        return full
     flat = torch.empty((sh.world * l, b, n), dtype=local.dtype, device=local.device)   # concatenation form
     # torch.uint64 is not accepted by every backend: gather the bit pattern as int64
     dist.all_gather_into_tensor(flat.view(torch.int64), local.contiguous().view(torch.int64), group=group)
     if sh.g_b == 1:
         return flat.reshape(sh.g_l * l, b, n)       # limb-outermost layout: no repacking needed
     return flat.reshape(sh.g_l, sh.g_b, l, b, n).permute(0, 2, 1, 3, 4).reshape(sh.g_l * l, sh.g_b * b, n)
+
+
+def all_gather_limb_async(local_k: torch.Tensor, full: torch.Tensor, k: int, sh: Shard, group=None):
+    """Cyclic map only: start the all-gather of every rank's k-th local limb ([B/g_b, N]) into full[k*g_l:(k+1)*g_l] and
+    return the work handle.  The collective is ordered after what the current stream has enqueued so far (the kernels that
+    produce local_k) and runs on the backend's own stream, so kernels launched next -- limb k+1 -- overlap it; call
+    .wait() on the handle before the current stream reads `full`.  Rank (i, j) of the (g_l x g_b) grid contributes limb
+    k*g_l + i, batch block j: chunk i*g_b + j = its rank, which is exactly where that block sits in the slab."""
+    import torch.distributed as dist
+    if not sh.cyclic:
+        raise ValueError("per-limb gathers land contiguously only with the cyclic limb map (partition(..., cyclic=True))")
+    slab = full[k * sh.g_l:(k + 1) * sh.g_l]
+    return dist.all_gather_into_tensor(slab.view(torch.int64).view(-1), local_k.contiguous().view(torch.int64).view(-1), group=group, async_op=True)
 
 
 def bind_to_gpu_numa(device_index: int):

@@ -111,3 +111,31 @@ def test_pipelined_config4_full_size(cuda_device, pipe_on):
     R = cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli])
     c = P.poly_mul(dev(a, cuda_device), dev(b, cuda_device), list(moduli))
     assert np.array_equal(host(c), R.poly_mul(a, b, fast=True, nthreads=16))
+
+
+@pytest.mark.parametrize("bits,packed", [(60, False), (50, False), (30, False), (30, True)])
+@pytest.mark.parametrize("logn,L,B", [(13, 2, 5), (14, 3, 4), (16, 5, 3), (16, 4, 16)])
+def test_two_stream_split_matches_oracle(cuda_device, monkeypatch, bits, packed, logn, L, B):
+    """plan.cu split_run: the limb range cut in two halves on two streams (forced here; by default only jobs of 512..4096 tiles
+    take it, which the last shape is).  Odd limb counts, every policy, and back-to-back calls that reuse the fork/join events."""
+    import polynomial as P
+    if not (L == 4 and B == 16):
+        monkeypatch.setenv("GFHE_SPLIT", "1")
+    P.clear_plans()
+    N = 1 << logn
+    moduli = P.ntt_primes(bits, L)
+    a, b = rand_lbn(3 * logn + bits, moduli, B, N), rand_lbn(3 * logn + bits + 1, moduli, B, N)
+    R = cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli])
+    ta, tb = dev(a, cuda_device, packed), dev(b, cuda_device, packed)
+    want_c, want_X = R.poly_mul(a, b, fast=True, nthreads=8), R.ntt(a, fast=True, nthreads=8)
+    with P.ring(moduli):
+        for _ in range(3):
+            X = P.NTT(ta)
+            c = P.poly_mul(ta, tb)
+            back = P.iNTT(X)
+            pre = P.poly_mul_pre(ta, P.NTT(tb))
+        assert np.array_equal(host(X), want_X)
+        assert np.array_equal(host(c), want_c)
+        assert torch.equal(back, ta)
+        assert np.array_equal(host(pre), want_c)
+    P.clear_plans()

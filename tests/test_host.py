@@ -175,6 +175,13 @@ def test_partition():
     assert len(cover) == 16
     with pytest.raises(ValueError):
         shard.partition(1, 3, 2, 0)
+    # cyclic limb map: rank i holds limbs i, i+g, ...; the k-th local limbs of all ranks are the slab [k*g, (k+1)*g)
+    s = [shard.partition(32, 16, 8, r, cyclic=True) for r in range(8)]
+    assert [x.limb_ids for x in s][:2] == [(0, 8, 16, 24), (1, 9, 17, 25)] and all(x.num_limbs == 4 for x in s)
+    for k in range(4):
+        assert sorted(x.limb_ids[k] for x in s) == list(range(8 * k, 8 * k + 8))
+    s = [shard.partition(2, 8, 8, r, cyclic=True) for r in range(8)]
+    assert sorted((x.limb_ids, x.batch) for x in s) == sorted(((i,), (2 * j, 2 * j + 2)) for i in range(2) for j in range(4))
 
 
 def test_numa_binding_helper_is_harmless_without_nvml(built_lib):

@@ -18,7 +18,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, L, B, N, q_bits, result_dir):
+def _worker(rank, world, port, L, B, N, q_bits, result_dir, cyclic=False):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import arithmetic  # noqa: F401
@@ -31,9 +31,9 @@ def _worker(rank, world, port, L, B, N, q_bits, result_dir):
     moduli = O.ntt_primes(q_bits, L)
     rng = np.random.default_rng(1234)          # same full input on every rank
     a = np.stack([rng.integers(0, q, (B, N), dtype=np.uint64) for q in moduli])
-    sh = shard.partition(L, B, world, rank)
+    sh = shard.partition(L, B, world, rank, cyclic=cyclic)
     mine = shard.take(torch.from_numpy(a.view(np.int64)), sh)
-    my_moduli = moduli[sh.limbs[0]:sh.limbs[1]]
+    my_moduli = [moduli[l] for l in sh.limb_ids]
     R = cref.Ring(N, my_moduli, [O.find_psi(q, N) for q in my_moduli])
     local = torch.from_numpy(R.ntt(mine.numpy().view(np.uint64)).view(np.int64))
     full = shard.all_gather_limbs(local, sh)
@@ -43,8 +43,11 @@ def _worker(rank, world, port, L, B, N, q_bits, result_dir):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("cyclic", [False, True])
 @pytest.mark.parametrize("world,L,B", [(2, 4, 3), (2, 1, 4), (4, 2, 4)])
-def test_sharded_ntt_allgather_gloo(tmp_path, world, L, B):
-    mp.spawn(_worker, args=(world, _free_port(), L, B, 64, 30, str(tmp_path)), nprocs=world, join=True)
+def test_sharded_ntt_allgather_gloo(tmp_path, world, L, B, cyclic):
+    """block map: one gather of the whole shard; cyclic map: one (asynchronous) gather per local limb, each landing in its
+    contiguous slab of the result"""
+    mp.spawn(_worker, args=(world, _free_port(), L, B, 64, 30, str(tmp_path), cyclic), nprocs=world, join=True)
     for r in range(world):
         assert open(tmp_path / ("rank%d" % r)).read() == "ok"

@@ -708,3 +708,27 @@ def test_empty_and_non_contiguous_operands(cuda_device):
         P.NTT(big, MOD=[q, q, q])              # three moduli, leading dimension 2
     with pytest.raises(RuntimeError):
         P.set_ring(None); P.NTT(x)             # no ring installed and no MOD=
+
+
+@pytest.mark.parametrize("L,B", [(1, 1), (64, 64)])
+def test_config5_extremes_n131072(cuda_device, L, B):
+    """BASELINE.json configs[4] end points: N = 2^17 forward NTT at [1,1] and [64,64] (4096 limb-NTTs, 4 GiB per buffer), every
+    word against the C oracle; the inverse must give the input back."""
+    import polynomial as P
+    N = 1 << 17
+    moduli = P.ntt_primes(60, L)
+    rng = np.random.default_rng(20261104 + 5)
+    x = np.empty((L, B, N), dtype=np.uint64)
+    for l, q in enumerate(moduli):
+        x[l] = rng.integers(0, q, (B, N), dtype=np.uint64)
+    x[:, 0, :4] = np.array(moduli, dtype=np.uint64).reshape(L, 1) - 1
+    tx = dev_i64(x, cuda_device)
+    with P.ring(moduli):
+        X = P.NTT(tx)
+        back = P.iNTT(X)
+    assert torch.equal(back, tx)
+    del back
+    got = host_u64(X)
+    del X
+    want = oracle_ring(N, moduli).ntt(x, fast=True, nthreads=32)
+    assert np.array_equal(got, want)

@@ -120,6 +120,80 @@ __device__ __forceinline__ u64 dfmul_split(const Split& y, u64 w0, u64 w1, doubl
         "}\n" : "=l"(r) : "r"(yl), "r"(yh), "l"(w0), "l"(w1), "l"(nq), "r"(hlo), "r"(hhi));
     return r;
 }
+// ---- round-2 candidates -------------------------------------------------------------------------------------------
+// Montgomery-friendly modulus q = 1 (mod 2^32): -q mod 2^64 = nh*2^32 + (2^32 - 1), so h*(-q) = h*(nh+1)*2^32 - h and the
+// IMAD.WIDE h0*nl plus the IMAD h1*nl of shoup_a become a 64-bit subtraction and a 32-bit one.  4 IMAD.WIDE + 3 IMAD.
+__device__ __forceinline__ u64 shoup_mf(u64 x, u64 w, u64 ws, u32 nhp1) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,wl,wh,pl,ph,h0,h1,top,lo,d;\n\t"
+        ".reg .u64 t1,t2,h,acc;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {wl,wh}, %2;\n\t"
+        "mov.b64 {pl,ph}, %3;\n\t"
+        "mul.wide.u32 t1, xl, ph;\n\t"
+        "mul.wide.u32 t2, xh, pl;\n\t"
+        "mov.b64 {d,h0}, t1;\n\t"
+        "mov.b64 {d,h1}, t2;\n\t"
+        "add.cc.u32 h0, h0, h1;\n\t"
+        "addc.u32 h1, 0, 0;\n\t"
+        "mov.b64 t1, {h0,h1};\n\t"
+        "mad.wide.u32 h, xh, ph, t1;\n\t"
+        "mov.b64 {h0,h1}, h;\n\t"
+        "mul.wide.u32 acc, xl, wl;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "sub.cc.u32 lo, lo, h0;\n\t"
+        "subc.u32 top, top, h1;\n\t"       // borrow and -h1 in one instruction
+        "mad.lo.u32 top, xl, wh, top;\n\t"
+        "mad.lo.u32 top, xh, wl, top;\n\t"
+        "mad.lo.u32 top, h0, %4, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n"
+        : "=l"(r)
+        : "l"(x), "l"(w), "l"(ws), "r"(nhp1));
+    return r;
+}
+// SURVEY 8d family q = 2^60 - c, c < 2^32: the high word of -q is 0xF0000000, so h0*nh is a shift.  5 IMAD.WIDE + 3 IMAD + shift-add.
+__device__ __forceinline__ u64 shoup_sol(u64 x, u64 w, u64 ws, u64 nq) {
+    u64 r;
+    asm("{\n\t"
+        ".reg .u32 xl,xh,wl,wh,pl,ph,nl,nh,h0,h1,top,lo,d,s;\n\t"
+        ".reg .u64 t1,t2,h,acc;\n\t"
+        "mov.b64 {xl,xh}, %1;\n\t"
+        "mov.b64 {wl,wh}, %2;\n\t"
+        "mov.b64 {pl,ph}, %3;\n\t"
+        "mov.b64 {nl,nh}, %4;\n\t"
+        "mul.wide.u32 t1, xl, ph;\n\t"
+        "mul.wide.u32 t2, xh, pl;\n\t"
+        "mov.b64 {d,h0}, t1;\n\t"
+        "mov.b64 {d,h1}, t2;\n\t"
+        "add.cc.u32 h0, h0, h1;\n\t"
+        "addc.u32 h1, 0, 0;\n\t"
+        "mov.b64 t1, {h0,h1};\n\t"
+        "mad.wide.u32 h, xh, ph, t1;\n\t"
+        "mov.b64 {h0,h1}, h;\n\t"
+        "mul.wide.u32 acc, xl, wl;\n\t"
+        "mad.wide.u32 acc, h0, nl, acc;\n\t"
+        "mov.b64 {lo,top}, acc;\n\t"
+        "mad.lo.u32 top, xl, wh, top;\n\t"
+        "mad.lo.u32 top, xh, wl, top;\n\t"
+        "shl.b32 s, h0, 28;\n\t"
+        "sub.u32 top, top, s;\n\t"          // h0 * 0xF0000000 = -(h0 << 28) mod 2^32
+        "mad.lo.u32 top, h1, nl, top;\n\t"
+        "mov.b64 %0, {lo,top};\n\t"
+        "}\n"
+        : "=l"(r)
+        : "l"(x), "l"(w), "l"(ws), "l"(nq));
+    return r;
+}
+// Montgomery product of two general residues (pointwise product with R^-1 left for the inverse's constants): a*b*2^-64 mod q
+// in [0, 2q) for a*b < q*2^64.  qinv = -q^-1 mod 2^64.  The low halves cancel exactly, so the carry is (z0 != 0).
+__device__ __forceinline__ u64 mont_mul(u64 a, u64 b, u64 q, u64 qinv) {
+    const u64 z0 = a * b, z1 = __umul64hi(a, b);
+    const u64 m = z0 * qinv;
+    return z1 + __umul64hi(m, q) + (z0 != 0);
+}
+
 // s = (a op b) + c on split halves, three-input 64-bit add with the result written into the low words of s's pairs
 __device__ __forceinline__ void split_add3(Split& s, u32 al, u32 ah, u64 t, u64 c, bool sub) {
     u32 lo, hi;
@@ -204,6 +278,16 @@ __global__ void __launch_bounds__(512, 2) kb(u64* out, long long* cyc, u64 q, u6
                 const u64 t = dfmul_cvt(Y[i], w, ws, r0, r1, nq);
                 const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i];
                 X[i] = x + t + q2; Y[i] = x - t + q4;
+            } else if (MODE == 15) {  // Montgomery-friendly prime (q = 1 mod 2^32), csub every 2nd
+                const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i], t = shoup_mf(Y[i], w, ws, (u32)(nq >> 32) + 1u);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 16) {  // SURVEY 8d family (high word of -q = 0xF0000000), csub every 2nd
+                const u64 x = (i & 1) ? csub(X[i], q4 + q4) : X[i], t = shoup_sol(Y[i], w, ws, nq);
+                X[i] = x + t; Y[i] = x - t + q4;
+            } else if (MODE == 17) {  // pointwise product as shipped: lazy single-mulhi Barrett, no final subtraction
+                Y[i] = barrett_lazy(Y[i] & 0x1fffffffffffffffull, X[i] & 0x1fffffffffffffffull, nq, ws, 59) + (u64)i;
+            } else if (MODE == 18) {  // pointwise product in Montgomery form
+                Y[i] = mont_mul(Y[i] & 0x1fffffffffffffffull, X[i] & 0x1fffffffffffffffull, q, ws | 1) + (u64)i;
             } else if (MODE == 7) {   // shoup_a alone
                 Y[i] = shoup_a(Y[i] + X[i], w, ws, nq);
             } else {                  // barrett product (pointwise)
@@ -331,6 +415,11 @@ int main(int argc, char** argv) {
     runf<0>("FP64 butterfly q<2^50, no range reduction", sms);
     runf<1>("FP64 butterfly q<2^50, reduce 1 in 4", sms);
     runf<1>("  same, 4 warps/SMSP", sms, 256);
+    run<15>("fwd  Montgomery-friendly q=1 mod 2^32, csub/2", sms);
+    run<15>("  same, 4 warps/SMSP", sms, 256);
+    run<16>("fwd  2^60-c family (shift for h0*nh), csub/2", sms);
+    run<17>("pointwise: lazy Barrett (shipped)", sms);
+    run<18>("pointwise: Montgomery form", sms);
     run<7>("shoup_a alone (+1 add)", sms);
     run<8>("barrett_mul (+2 csub)", sms);
     return 0;

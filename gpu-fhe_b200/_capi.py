@@ -51,6 +51,11 @@ SYMBOLS = {
     "gfhe_automorphism_u32": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
     "gfhe_ntt_mul_acc": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, u32, vp, vp, ctypes.c_uint64, vp, vp]),
     "gfhe_automorphism": (ctypes.c_int, [vp, u32, u32, u32, u32, ctypes.c_int, vp, vp, vp]),
+    "gfhe_peer_alloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_size_t, ctypes.POINTER(vp), ctypes.c_char_p]),
+    "gfhe_peer_open": (ctypes.c_int, [ctypes.c_int, ctypes.c_char_p, ctypes.POINTER(vp)]),
+    "gfhe_peer_close": (ctypes.c_int, [ctypes.c_int, vp]),
+    "gfhe_peer_free": (ctypes.c_int, [ctypes.c_int, vp]),
+    "gfhe_push_gather": (ctypes.c_int, [ctypes.c_int, vp, ctypes.c_size_t, ctypes.POINTER(vp), u32, ctypes.c_size_t, u32, vp]),
     "gfhe_ntt_host": (ctypes.c_int, [vp, ctypes.c_int, u32, vp, vp]),
     "gfhe_poly_mul_host": (ctypes.c_int, [vp, u32, vp, vp, vp]),
     "gfhe_debug_pipe_schedule": (ctypes.c_int, [u32, ctypes.POINTER(u32), u32, u32, ctypes.POINTER(u32), u32, ctypes.POINTER(u32)]),
@@ -77,7 +82,7 @@ for _name, (_res, _args) in SYMBOLS.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 if lib.gfhe_abi_version() != ABI_VERSION:
     raise ImportError("gpufhe_b200: ABI version mismatch (library %d, binding %d)" % (lib.gfhe_abi_version(), ABI_VERSION))
 

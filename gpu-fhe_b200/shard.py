@@ -14,7 +14,7 @@ gather can be issued limb by limb, each one overlapping the next limb's kernels
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Tuple
+from typing import Optional, Tuple
 
 import torch
 
@@ -99,6 +99,118 @@ def all_gather_limb_async(local_k: torch.Tensor, full: torch.Tensor, k: int, sh:
         raise ValueError("per-limb gathers land contiguously only with the cyclic limb map (partition(..., cyclic=True))")
     slab = full[k * sh.g_l:(k + 1) * sh.g_l]
     return dist.all_gather_into_tensor(slab.view(torch.int64).view(-1), local_k.contiguous().view(torch.int64).view(-1), group=group, async_op=True)
+
+
+class PeerGather:
+    """The all-gather of result limbs as NVLink peer stores issued by the library (csrc/gather.cu, gfhe_push_gather) instead of
+    an NCCL all-gather after the kernels.
+
+    Every rank owns a full [L, B, N] result array in peer-mappable memory (`.full`, a torch view of it); the ranks exchange
+    CUDA IPC handles once (all_gather_object) and map each other's arrays.  `push(local, sh)` copies this rank's block --
+    or, limb by limb, `push_limb(local, k, sh)` -- into the same position of every rank's array, asynchronously on the
+    current stream (enqueue it behind the kernels of limb k and limb k+1's kernels overlap it).  `finish()` is the one point
+    of cross-rank synchronisation: a stream-ordered all-reduce of a flag, which every rank enters after its own pushes, so
+    when it completes on a rank every peer's block has landed there.  No kernel waits for another GPU.
+    """
+
+    def __init__(self, L: int, B: int, N: int, device: torch.device, group=None, word_bytes: int = 8):
+        import ctypes
+        import torch.distributed as dist
+        from . import _capi
+        self._capi, self._ct, self._dist = _capi, ctypes, dist
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world > 16:
+            raise ValueError("PeerGather serves the GPUs of one box (at most 16)")
+        self.dev = torch.device(device)
+        self.shape, self.word = (int(L), int(B), int(N)), int(word_bytes)
+        self.bytes = L * B * N * word_bytes
+        own = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        _capi.check(_capi.lib.gfhe_peer_alloc(self.dev.index, self.bytes, ctypes.byref(own), handle), "gfhe_peer_alloc")
+        self._own = own
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self._peers = []
+        bases = []
+        for r in range(self.world):
+            if r == self.rank:
+                bases.append(own.value)
+                continue
+            p = ctypes.c_void_p()
+            _capi.check(_capi.lib.gfhe_peer_open(self.dev.index, handles[r], ctypes.byref(p)), "gfhe_peer_open")
+            self._peers.append(p)
+            bases.append(p.value)
+        self._bases = (ctypes.c_void_p * self.world)(*bases)
+        others = [b for r, b in enumerate(bases) if r != self.rank]
+        self._others = (ctypes.c_void_p * max(1, len(others)))(*others)
+        self.full = self._view(own.value)
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.dev)
+
+    def _view(self, ptr: int) -> torch.Tensor:
+        dt = torch.int64 if self.word == 8 else torch.int32
+        typestr = "<i8" if self.word == 8 else "<i4"
+
+        class _Mem:      # CUDA array interface over the raw allocation
+            __cuda_array_interface__ = {"shape": self.shape, "typestr": typestr, "data": (ptr, False), "version": 3}
+        t = torch.as_tensor(_Mem(), device=self.dev)
+        assert t.dtype == dt and t.data_ptr() == ptr
+        return t
+
+    def local_block(self, sh: "Shard") -> Optional[torch.Tensor]:
+        """This rank's block as a view INTO its own full array, when the block is contiguous there (block limb map, no
+        batch split): have the kernels write their result here and the push need not copy it to this rank itself."""
+        if sh.cyclic or sh.g_b != 1:
+            return None
+        return self.full[sh.limbs[0]:sh.limbs[1]]
+
+    def _in_place(self, src: torch.Tensor, offset_bytes: int) -> bool:
+        return src.data_ptr() == self._own.value + offset_bytes
+
+    def _push(self, src: torch.Tensor, offset_bytes: int, ctas: int = 0) -> None:
+        st = self._ct.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
+        # a block that already sits in this rank's array (local_block) goes to the peers only
+        bases, n = (self._others, self.world - 1) if self._in_place(src, offset_bytes) else (self._bases, self.world)
+        if n == 0:
+            return
+        self._capi.check(self._capi.lib.gfhe_push_gather(self.dev.index, self._ct.c_void_p(src.data_ptr()), src.numel() * src.element_size(),
+                                                         bases, n, offset_bytes, int(ctas), st), "gfhe_push_gather")
+
+    OVERLAP_CTAS = 32      # copy CTAs of a push that runs under other kernels (measured: csrc/gather.cu)
+
+    def push_limb(self, local: torch.Tensor, k: int, sh: "Shard", ctas: Optional[int] = None) -> None:
+        """Local limb k ([B/g_b, N], contiguous) of this rank's result into its place in every rank's array.  Meant to be
+        enqueued on a side stream behind limb k's kernels, so by default it runs on few CTAs."""
+        L, B, N = self.shape
+        limb = sh.limb_ids[k]
+        self._push(local[k], ((limb * B + sh.batch[0]) * N) * self.word, self.OVERLAP_CTAS if ctas is None else ctas)
+
+    def push(self, local: torch.Tensor, sh: "Shard") -> None:
+        """The whole local block [L/g_l, B/g_b, N]: one copy when it is contiguous in the result, else limb by limb."""
+        L, B, N = self.shape
+        if not sh.cyclic and sh.g_b == 1:
+            self._push(local, (sh.limbs[0] * B * N) * self.word)
+        else:
+            for k in range(local.shape[0]):
+                self.push_limb(local, k, sh, ctas=0)
+
+    def finish(self) -> None:
+        """Stream-ordered: when this returns control to the stream, every rank's pushes issued before its own finish() have landed."""
+        self._dist.all_reduce(self._flag, group=self.group)
+
+    def close(self) -> None:
+        if getattr(self, "_own", None) is None:
+            return
+        torch.cuda.synchronize(self.dev)
+        self._dist.barrier(group=self.group)          # nobody unmaps or frees while a peer may still be pushing
+        for p in self._peers:
+            self._capi.lib.gfhe_peer_close(self.dev.index, p)
+        self._peers = []
+        self._dist.barrier(group=self.group)
+        self.full = None
+        self._capi.lib.gfhe_peer_free(self.dev.index, self._own)
+        self._own = None
 
 
 def bind_to_gpu_numa(device_index: int):

@@ -38,7 +38,7 @@
 extern "C" {
 #endif
 
-#define GFHE_ABI_VERSION 4
+#define GFHE_ABI_VERSION 5
 
 #define GFHE_EARG      (-1)   /* null pointer / zero size */
 #define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
@@ -161,6 +161,24 @@ int gfhe_ntt_mul_acc(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint6
  * gfhe_ntt_forward (pure permutation), so that automorphism(NTT(a)) == NTT(automorphism(a)).  Out of place. */
 int gfhe_automorphism(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch, uint32_t k, int ntt_domain,
                       const uint64_t* d_in, uint64_t* d_out, void* stream);
+
+/* The path's one collective, the all-gather of result limbs to every GPU of one box, as NVLink peer stores issued by the
+ * library (gather.cu) instead of a separate NCCL call.  One process per GPU: each rank allocates its full [L, B, N] result
+ * array with gfhe_peer_alloc, which also returns a 64-byte CUDA IPC handle; the ranks exchange the handles (any transport)
+ * and open each other's arrays with gfhe_peer_open.  gfhe_push_gather then copies `bytes` from d_src (this rank's result
+ * block, or one limb of it) to offset dst_offset_bytes of every array in dst_bases (host array of ndst <= GFHE_MAX_PEERS
+ * device pointers: the peers', and this rank's own if it wants the block there too), asynchronously on `stream` -- so it
+ * can follow each limb's kernels while the next limb is computed.  It never waits for another GPU; the caller orders
+ * "all pushes have landed" with one stream-ordered collective of its own after the last push (shard.py, PeerGather).
+ * `ctas` caps the copy kernel's grid: 0 = one CTA per SM (fastest alone), about 32 when the push overlaps other kernels.
+ * Pointers, sizes and offsets must be multiples of 16 bytes (GFHE_EALIGN). */
+#define GFHE_MAX_PEERS 16
+int gfhe_peer_alloc(int device, size_t bytes, void** d_ptr, unsigned char* handle64);
+int gfhe_peer_open(int device, const unsigned char* handle64, void** d_ptr);
+int gfhe_peer_close(int device, void* d_ptr);
+int gfhe_peer_free(int device, void* d_ptr);
+int gfhe_push_gather(int device, const void* d_src, size_t bytes, void* const* dst_bases, uint32_t ndst,
+                     size_t dst_offset_bytes, uint32_t ctas, void* stream);
 
 /* Host-buffer variants: h_* are host arrays [L, batch, N] covering ALL limbs of the plan.  Limb groups are streamed
  * H2D -> kernels -> D2H on separate streams so copies overlap compute.  Pinned arrays are copied from / to in place;

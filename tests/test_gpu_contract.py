@@ -341,3 +341,88 @@ def test_multi_gpu_sharded_poly_mul_all_gather(cuda_device, tmp_path, L, B, N, b
     mp.spawn(_mgpu_worker, args=(world, _free_port(), L, B, N, bits, str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
         assert open(tmp_path / ("rank%d" % r)).read() == "ok", r
+
+
+def _peer_worker(rank, world, port, L, B, N, bits, result_dir):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import torch.distributed as dist
+
+    import polynomial as P
+    from gpu_fhe_b200 import shard
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    moduli = P.ntt_primes(bits, L)
+
+    def block(l, which):
+        return np.random.default_rng([77, which, l]).integers(0, moduli[l], (B, N), dtype=np.uint64)
+    fa = np.stack([block(l, 0) for l in range(L)])
+    fb = np.stack([block(l, 1) for l in range(L)])
+    want = cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli]).poly_mul(fa, fb, fast=True, nthreads=4)
+    ok = True
+    for cyclic in (False, True):
+        sh = shard.partition(L, B, world, rank, cyclic=cyclic)
+        ids = sh.limb_ids
+        a = np.stack([fa[l, sh.batch[0]:sh.batch[1]] for l in ids])
+        b = np.stack([fb[l, sh.batch[0]:sh.batch[1]] for l in ids])
+        mine = [moduli[l] for l in ids]
+        pg = shard.PeerGather(L, B, N, dev)
+        # (1) the whole block after the product
+        local = P.poly_mul(dev_i64(a, dev), dev_i64(b, dev), mine)
+        pg.full.zero_()
+        torch.cuda.synchronize(); dist.barrier()
+        pg.push(local, sh)
+        pg.finish()
+        torch.cuda.synchronize()
+        ok = ok and np.array_equal(host_u64(pg.full), want)
+        # (1b) the block produced in place inside this rank's own array: pushed to the peers only
+        blk = pg.local_block(sh)
+        ok = ok and ((blk is None) == (cyclic or sh.g_b != 1))
+        if blk is not None:
+            dist.barrier()
+            pg.full.zero_()
+            torch.cuda.synchronize(); dist.barrier()
+            blk.copy_(local)
+            pg.push(blk, sh)
+            pg.finish()
+            torch.cuda.synchronize()
+            ok = ok and np.array_equal(host_u64(pg.full), want)
+        # (2) limb by limb on a side stream while the next limb is multiplied
+        dist.barrier()
+        pg.full.zero_()
+        torch.cuda.synchronize(); dist.barrier()
+        side = torch.cuda.Stream(dev)
+        outs = []
+        for k in range(len(ids)):
+            ck = P.poly_mul(dev_i64(a[k:k + 1], dev), dev_i64(b[k:k + 1], dev), [mine[k]])
+            outs.append(ck)
+            ev = torch.cuda.Event(); ev.record()
+            side.wait_event(ev)
+            with torch.cuda.stream(side):
+                pg.push_limb(ck, 0, shard.Shard(sh.rank, sh.world, sh.g_l, sh.g_b, (ids[k], ids[k] + 1), sh.batch))
+        ev = torch.cuda.Event(); ev.record(side)
+        torch.cuda.current_stream().wait_event(ev)
+        pg.finish()
+        torch.cuda.synchronize()
+        ok = ok and np.array_equal(host_u64(pg.full), want)
+        pg.close()
+    open(os.path.join(result_dir, "rank%d" % rank), "w").write("ok" if ok else "bad")
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("L,B,N,bits", [(8, 2, 8192, 60), (2, 8, 4096, 50)])
+def test_multi_gpu_peer_store_gather(cuda_device, tmp_path, L, B, N, bits):
+    """The library's own all-gather (NVLink peer stores, csrc/gather.cu through shard.PeerGather): block and cyclic limb maps,
+    limb-and-batch shards, whole-block and limb-by-limb pushes; every rank's full array against the oracle."""
+    world = min(torch.cuda.device_count(), 8)
+    while world > 1 and (L * B) % world:
+        world -= 1
+    if world < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    mp.spawn(_peer_worker, args=(world, _free_port(), L, B, N, bits, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert open(tmp_path / ("rank%d" % r)).read() == "ok", r

@@ -513,8 +513,17 @@ def run_b200(args, rank, world, local_rank):
     # ---- the gather as NVLink peer stores issued by the library itself (csrc/gather.cu, shard.PeerGather): each rank pushes its
     # block into every rank's full array; one stream-ordered flag all-reduce closes the step.  Whole block after the kernels,
     # and chunk by chunk on a side stream while the next chunk is multiplied.
+    pgx, peer_err = None, None
     if world > 1:
-        pgx = shard.PeerGather(L_TOTAL, B_TOTAL, N, dev)
+        try:                                          # CUDA IPC between the ranks' processes: report, do not die, if a box forbids it
+            pgx = shard.PeerGather(L_TOTAL, B_TOTAL, N, dev)
+        except Exception as exc:   # noqa: BLE001
+            peer_err = "%s: %s" % (type(exc).__name__, exc)
+            log("peer-store gather unavailable on rank %d: %s" % (rank, peer_err))
+        if not cx.all_true(pgx is not None):          # all ranks or none (close() is collective: a rank that got one just drops it)
+            pgx = None
+            gather["peer_store"] = {"error": peer_err or "unavailable on another rank"}
+    if pgx is not None:
         side = torch.cuda.Stream(dev)
         limb_bytes = nb * N * 8
 
@@ -591,8 +600,8 @@ def run_b200(args, rank, world, local_rank):
                                         "[32,16,65536] array, then one flag all-reduce; overlapped = chunk k pushed on a side stream under chunk k+1's kernels"}
         del got, ref_full, mine
         pgx.close()
-        if rank == 0:
-            del want_full
+    if world > 1 and rank == 0:
+        del want_full
 
     # ---- round 1's weak-scaling variant (per-GPU work fixed at 512 units: 32/n limbs x 16n batch per rank)
     weak = None
@@ -798,7 +807,7 @@ def run_b200(args, rank, world, local_rank):
         "config": workload_config(world),
         "full_rns_poly_mul_per_s": value / L_TOTAL,
         "value_with_gather": UNITS_TOTAL / (min(gather["step_with_gather_ms"], gather.get("step_with_overlapped_gather_ms", 1e30),
-                                                     gather["peer_store"]["step_with_gather_ms"], gather["peer_store"]["step_with_overlapped_gather_ms"]) * 1e-3) if gather else value,
+                                                     gather["peer_store"].get("step_with_gather_ms", 1e30), gather["peer_store"].get("step_with_overlapped_gather_ms", 1e30)) * 1e-3) if gather else value,
         "parity": parity,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak if achieved else None, "traffic": ncu_traffic(dom) if world == 1 else None,

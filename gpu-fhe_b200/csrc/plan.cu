@@ -339,14 +339,16 @@ static cudaError_t do_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64*
 // full [32,16,65536] the grids are 14-28 waves deep and the split gains nothing, so it is applied to small jobs only.
 // GFHE_SPLIT=0 / 1 at plan creation: never / whenever there are two limbs.
 static bool want_split(const Plan& pl, u32 nl, u32 B) {
-    if (pl.split == 0 || pl.logN <= 12 || nl < 2 || pl.pipe == 1) return false;
+    if (pl.split == 0 || pl.logN <= 12 || (nl < 2 && B < 2) || pl.pipe == 1) return false;
     if (pl.split == 1) return true;
     const u64 tiles = ((u64)nl * B) << (pl.logN - 12);
     return tiles >= 512 && tiles <= 4096;
 }
-template <class F>   // run(limb0, nl, offset of the range in limb-rows, stream)
+// run(first limb, limbs, batch of this half, offset of the half in polynomials, stream).  Two or more limbs: cut between limbs;
+// a single limb: cut its batch.
+template <class F>
 static cudaError_t split_run(const Plan& pl, u32 limb0, u32 nl, u32 B, cudaStream_t st, F run) {
-    if (!want_split(pl, nl, B)) return run(limb0, nl, 0u, st);
+    if (!want_split(pl, nl, B)) return run(limb0, nl, B, (size_t)0, st);
     std::lock_guard<std::mutex> lock(pl.sync_mu);   // the fork / join events are the plan's: one enqueue sequence at a time
     cudaError_t e;
     if (!pl.aux_stream) {
@@ -354,11 +356,17 @@ static cudaError_t split_run(const Plan& pl, u32 limb0, u32 nl, u32 B, cudaStrea
         if ((e = cudaEventCreateWithFlags(&pl.ev_fork, cudaEventDisableTiming))) return e;
         if ((e = cudaEventCreateWithFlags(&pl.ev_join, cudaEventDisableTiming))) return e;
     }
-    const u32 h = nl / 2;
     if ((e = cudaEventRecord(pl.ev_fork, st))) return e;
     if ((e = cudaStreamWaitEvent(pl.aux_stream, pl.ev_fork, 0))) return e;
-    if ((e = run(limb0, h, 0u, st))) return e;
-    e = run(limb0 + h, nl - h, h, pl.aux_stream);
+    if (nl >= 2) {
+        const u32 h = nl / 2;
+        if ((e = run(limb0, h, B, (size_t)0, st))) return e;
+        e = run(limb0 + h, nl - h, B, (size_t)h * B, pl.aux_stream);
+    } else {
+        const u32 h = B / 2;
+        if ((e = run(limb0, 1u, h, (size_t)0, st))) return e;
+        e = run(limb0, 1u, B - h, (size_t)h, pl.aux_stream);
+    }
     // join even after a failed launch: the caller's stream must not run ahead of what was enqueued on the other one
     cudaError_t e2 = cudaEventRecord(pl.ev_join, pl.aux_stream);
     if (e2 == cudaSuccess) e2 = cudaStreamWaitEvent(st, pl.ev_join, 0);
@@ -366,43 +374,43 @@ static cudaError_t split_run(const Plan& pl, u32 limb0, u32 nl, u32 B, cudaStrea
 }
 
 cudaError_t launch_ntt_fwd(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_ntt(pl, false, l0, n, in + off * row, out + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 b, size_t off, cudaStream_t s) { return do_ntt(pl, false, l0, n, in + (off << lg), out + (off << lg), b, s); });
 }
 cudaError_t launch_ntt_inv(const Plan& pl, u32 limb0, u32 nl, const u64* in, u64* out, u32 B, cudaStream_t st) {
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_ntt(pl, true, l0, n, in + off * row, out + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 b, size_t off, cudaStream_t s) { return do_ntt(pl, true, l0, n, in + (off << lg), out + (off << lg), b, s); });
 }
 cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u64* ws, u32 B, cudaStream_t st) {
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) {
-        return do_poly_mul(pl, l0, n, a + off * row, b + off * row, c + off * row, ws ? ws + off * row : nullptr, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 bb, size_t off, cudaStream_t s) {
+        return do_poly_mul(pl, l0, n, a + (off << lg), b + (off << lg), c + (off << lg), ws ? ws + (off << lg) : nullptr, bb, s); });
 }
 cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st) {
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return do_poly_mul_pre(pl, l0, n, a + off * row, b_ntt + off * row, c + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 bb, size_t off, cudaStream_t s) { return do_poly_mul_pre(pl, l0, n, a + (off << lg), b_ntt + (off << lg), c + (off << lg), bb, s); });
 }
 // packed layout: only plans on the 32-bit policy have it (every modulus below 2^30)
 cudaError_t launch_ntt_fwd_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
     if (!pl.w32) return cudaErrorNotSupported;
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_fwd(pl, l0, n, in + off * row, out + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 b, size_t off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_fwd(pl, l0, n, in + (off << lg), out + (off << lg), b, s); });
 }
 cudaError_t launch_ntt_inv_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st) {
     if (!pl.w32) return cudaErrorNotSupported;
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_inv(pl, l0, n, in + off * row, out + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 b, size_t off, cudaStream_t s) { return Launcher<Shoup32P>::ntt_inv(pl, l0, n, in + (off << lg), out + (off << lg), b, s); });
 }
 cudaError_t launch_poly_mul_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b, u32* c, u32* ws, u32 B, cudaStream_t st) {
     if (!pl.w32) return cudaErrorNotSupported;
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) {
-        return Launcher<Shoup32P>::poly_mul(pl, l0, n, a + off * row, b + off * row, c + off * row, ws ? ws + off * row : nullptr, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 bb, size_t off, cudaStream_t s) {
+        return Launcher<Shoup32P>::poly_mul(pl, l0, n, a + (off << lg), b + (off << lg), c + (off << lg), ws ? ws + (off << lg) : nullptr, bb, s); });
 }
 cudaError_t launch_poly_mul_pre_u32(const Plan& pl, u32 limb0, u32 nl, const u32* a, const u32* b_ntt, u32* c, u32 B, cudaStream_t st) {
     if (!pl.w32) return cudaErrorNotSupported;
-    const size_t row = (size_t)B << pl.logN;
-    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 off, cudaStream_t s) { return Launcher<Shoup32P>::poly_mul_pre(pl, l0, n, a + off * row, b_ntt + off * row, c + off * row, B, s); });
+    const u32 lg = pl.logN;
+    return split_run(pl, limb0, nl, B, st, [&](u32 l0, u32 n, u32 bb, size_t off, cudaStream_t s) { return Launcher<Shoup32P>::poly_mul_pre(pl, l0, n, a + (off << lg), b_ntt + (off << lg), c + (off << lg), bb, s); });
 }
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
     if (pl.logN <= 12) return 0;

@@ -114,12 +114,12 @@ def test_pipelined_config4_full_size(cuda_device, pipe_on):
 
 
 @pytest.mark.parametrize("bits,packed", [(60, False), (50, False), (30, False), (30, True)])
-@pytest.mark.parametrize("logn,L,B", [(13, 2, 5), (14, 3, 4), (16, 5, 3), (16, 4, 16)])
+@pytest.mark.parametrize("logn,L,B", [(13, 2, 5), (14, 3, 4), (16, 5, 3), (16, 4, 16), (14, 1, 7), (17, 1, 16)])
 def test_two_stream_split_matches_oracle(cuda_device, monkeypatch, bits, packed, logn, L, B):
     """plan.cu split_run: the limb range cut in two halves on two streams (forced here; by default only jobs of 512..4096 tiles
     take it, which the last shape is).  Odd limb counts, every policy, and back-to-back calls that reuse the fork/join events."""
     import polynomial as P
-    if not (L == 4 and B == 16):
+    if not ((L == 4 and B == 16) or (L == 1 and B == 16)):      # those two take the split by size (1024 / 512 tiles)
         monkeypatch.setenv("GFHE_SPLIT", "1")
     P.clear_plans()
     N = 1 << logn

@@ -97,8 +97,7 @@ int gfhe_push_gather(int device, const void* d_src, size_t bytes, void* const* d
     // alone, one CTA per SM is fastest (0.372 ms; 0.404 with 32 CTAs, 0.416 with 592); pushed limb by limb UNDER the next limb's
     // kernels, 32 CTAs are (0.474 ms per step against 0.550 with 148) -- every resident copy CTA takes an SM slot away from
     // the transforms.  `ctas` = 0: one per SM; the caller passes 32 for pushes it overlaps.  GFHE_PUSH_CTAS overrides both.
-    static int ctas_env = -1;
-    if (ctas_env < 0) { const char* env = std::getenv("GFHE_PUSH_CTAS"); ctas_env = env ? std::atoi(env) : 0; }
+    static const int ctas_env = [] { const char* env = std::getenv("GFHE_PUSH_CTAS"); return env ? std::atoi(env) : 0; }();
     size_t cap = ctas_env > 0 ? (size_t)ctas_env : (ctas ? (size_t)ctas : (size_t)sms);
     size_t blocks = (n16 + 256 * 4 - 1) / (256 * 4);
     if (blocks > cap) blocks = cap;

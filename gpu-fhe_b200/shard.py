@@ -200,6 +200,7 @@ class PeerGather:
         self._dist.all_reduce(self._flag, group=self.group)
 
     def close(self) -> None:
+        """Collective: every rank of the group must call it (peers unmap each other's arrays before any of them is freed)."""
         if getattr(self, "_own", None) is None:
             return
         torch.cuda.synchronize(self.dev)

@@ -27,10 +27,14 @@ __device__ __forceinline__ u32 ld_acquire_gpu(const u32* p) {
     return v;
 }
 
-// thread 0: draw the next ticket, decode it and wait for the tiles it consumes
-__device__ __forceinline__ void pipe_next(const PipeSched& sc, u32* sync, volatile u32* job) {
-    const u32 t = atomicAdd(sync, 1u);
-    if (t >= sc.total) { job[0] = sc.nph; return; }
+// thread 0: decode ticket t and wait for the tiles it consumes; then draw the NEXT ticket at once -- its L2 round trip runs
+// under this tile's work instead of between two tiles (the value is first looked at on the next trip)
+// PREFETCH = false (the product kernel, whose fused row pass has no register to spare for a value that lives across the
+// tile): the ticket is drawn here instead, `t` is ignored.
+template <bool PREFETCH>
+__device__ __forceinline__ u32 pipe_next(const PipeSched& sc, u32* sync, volatile u32* job, u32 t) {
+    if constexpr (!PREFETCH) t = atomicAdd(sync, 1u);
+    if (t >= sc.total) { job[0] = sc.nph; return t; }
     u32 pass, poly, w;
     pipe_decode(sc, t, &pass, &poly, &w);
     job[0] = pass; job[1] = poly; job[2] = w;
@@ -45,16 +49,21 @@ __device__ __forceinline__ void pipe_next(const PipeSched& sc, u32* sync, volati
         }
         asm volatile("fence.proxy.async;" ::: "memory");   // the producers used generic stores; this thread may read them by TMA next
     }
+    if constexpr (PREFETCH) return atomicAdd(sync, 1u);
+    else return 0u;
 }
 
-// every thread, after its tile: make the tile's global stores visible, then (thread 0) count the tile
+// after a tile: the barrier orders every thread's global stores before thread 0's fence (cumulativity -- the pattern of a
+// cooperative-groups grid barrier), and thread 0 alone releases them and counts the tile
 // (pass and polynomial are read back from the job words rather than kept in registers across the tile body)
 __device__ __forceinline__ void pipe_done(const PipeSched& sc, u32* sync, const volatile u32* job) {
-    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
         const u32 pass = job[0], poly = job[1];
-        if (pass + 1 < sc.nph) atomicAdd(sync + 2 + (size_t)pass * sc.npoly + poly, 1u);
+        if (pass + 1 < sc.nph) {
+            __threadfence();
+            atomicAdd(sync + 2 + (size_t)pass * sc.npoly + poly, 1u);
+        }
     }
 }
 
@@ -85,8 +94,9 @@ k_pipe_ntt_fwd(const typename A::store* in, typename A::store* out, const Tables
     __shared__ __align__(16) W sm[padded_words(12)];
     __shared__ typename A::tw_t tws[256];
     __shared__ u32 job[3];
+    u32 ticket = threadIdx.x == 0 ? atomicAdd(sync, 1u) : 0u;
     for (;;) {
-        if (threadIdx.x == 0) pipe_next(sc, sync, job);
+        if (threadIdx.x == 0) ticket = pipe_next<true>(sc, sync, job, ticket);
         __syncthreads();
         const u32 pass = job[0], flat = (job[1] << LT) + job[2];
         if (pass >= 2) break;
@@ -106,8 +116,9 @@ k_pipe_ntt_inv(const typename A::store* in, typename A::store* out, const Tables
     __shared__ __align__(16) W sm[padded_words(12)];
     __shared__ typename A::tw_t tws[256];
     __shared__ u32 job[3];
+    u32 ticket = threadIdx.x == 0 ? atomicAdd(sync, 1u) : 0u;
     for (;;) {
-        if (threadIdx.x == 0) pipe_next(sc, sync, job);
+        if (threadIdx.x == 0) ticket = pipe_next<true>(sc, sync, job, ticket);
         __syncthreads();
         const u32 pass = job[0], flat = (job[1] << LT) + job[2];
         if (pass >= 2) break;
@@ -140,7 +151,7 @@ k_pipe_polymul(const typename A::store* a, const typename A::store* b, typename 
     }
 #pragma unroll 1
     for (;;) {
-        if (threadIdx.x == 0) pipe_next(sc, sync, job);
+        if (threadIdx.x == 0) pipe_next<false>(sc, sync, job, 0u);
         __syncthreads();
         const u32 pass = job[0], poly = job[1], w = job[2];
         if (pass >= 3) break;

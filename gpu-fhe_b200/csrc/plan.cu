@@ -342,7 +342,8 @@ static bool want_split(const Plan& pl, u32 nl, u32 B) {
     if (pl.split == 0 || pl.logN <= 12 || (nl < 2 && B < 2) || pl.pipe == 1) return false;
     if (pl.split == 1) return true;
     const u64 tiles = ((u64)nl * B) << (pl.logN - 12);
-    return tiles >= 512 && tiles <= 4096;
+    if (tiles > 4096) return pl.w32 && nl >= 4;     // large jobs: the L2-sized chunk schedule, 32-bit words only (split_run)
+    return tiles >= 512;
 }
 // run(first limb, limbs, batch of this half, offset of the half in polynomials, stream).  Two or more limbs: cut between limbs;
 // a single limb: cut its batch.
@@ -358,7 +359,20 @@ static cudaError_t split_run(const Plan& pl, u32 limb0, u32 nl, u32 B, cudaStrea
     }
     if ((e = cudaEventRecord(pl.ev_fork, st))) return e;
     if ((e = cudaStreamWaitEvent(pl.aux_stream, pl.ev_fork, 0))) return e;
-    if (nl >= 2) {
+    const u64 limb_tiles = (u64)B << (pl.logN - 12);
+    if (pl.split < 0 && limb_tiles * nl > 4096) {
+        // large job on 32-bit words (want_split): chunks of about 2048 tiles alternate between the two streams, so a chunk's
+        // inter-pass words are re-read while they are still in L2 and each stream's launch tails are filled by the other's
+        // kernels.  Measured at [32,16,65536] (profiles/r02_run3_chunk_probe.txt, 8-limb chunks): 30-bit product 0.463 ->
+        // 0.442 ms, packed 0.359 -> 0.339 ms, NTT -3 %; nothing for 60-bit limbs (issue-bound), which is why they are excluded.
+        u32 cl = (u32)(2048 / (limb_tiles ? limb_tiles : 1));
+        if (cl < 1) cl = 1;
+        u32 k = 0;
+        for (u32 l = 0; l < nl && e == cudaSuccess; l += cl, ++k) {
+            const u32 n = nl - l < cl ? nl - l : cl;
+            e = run(limb0 + l, n, B, (size_t)l * B, (k & 1) ? pl.aux_stream : st);
+        }
+    } else if (nl >= 2) {
         const u32 h = nl / 2;
         if ((e = run(limb0, h, B, (size_t)0, st))) return e;
         e = run(limb0 + h, nl - h, B, (size_t)h * B, pl.aux_stream);

@@ -139,3 +139,25 @@ def test_two_stream_split_matches_oracle(cuda_device, monkeypatch, bits, packed,
         assert torch.equal(back, ta)
         assert np.array_equal(host(pre), want_c)
     P.clear_plans()
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_chunk_schedule_of_large_32bit_jobs(cuda_device, packed):
+    """plan.cu split_run, large jobs on 32-bit words (> 4096 tiles, >= 4 limbs): chunks of ~2048 tiles alternate between two
+    streams.  [6, 48, 65536] is 4608 tiles -> three 2-limb chunks; every word against the oracle, twice in a row."""
+    import polynomial as P
+    P.clear_plans()
+    N, L, B = 1 << 16, 6, 48
+    moduli = P.ntt_primes(30, L)
+    a, b = rand_lbn(11, moduli, B, N), rand_lbn(12, moduli, B, N)
+    R = cref.Ring(N, moduli, [O.find_psi(q, N) for q in moduli])
+    ta, tb = dev(a, cuda_device, packed), dev(b, cuda_device, packed)
+    want_c, want_X = R.poly_mul(a, b, fast=True, nthreads=16), R.ntt(a, fast=True, nthreads=16)
+    with P.ring(moduli):
+        for _ in range(2):
+            X = P.NTT(ta)
+            c = P.poly_mul(ta, tb)
+            assert np.array_equal(host(X), want_X)
+            assert np.array_equal(host(c), want_c)
+            assert torch.equal(P.iNTT(X), ta)
+    P.clear_plans()

@@ -17,6 +17,11 @@
  *   gfhe_automorphism            <- absent from the reference: a(X) -> a(X^k)
  *   gfhe_*_host                  <- the same calls made with host (numpy) arrays, as the reference's
  *                                   callers would make them; copies are pipelined inside the call
+ *   gfhe_vec_*_u64               <- /root/reference/arithmetic.py:3-13 on uint64 containers (values >= 2^63 are positive)
+ *   gfhe_plan_export / _import   <- the table cache /root/reference/primitive.py:3-4 was the placeholder for, in a
+ *                                   serialisable form
+ *   gfhe_peer_*, gfhe_push_gather <- absent from the reference (no collective of any kind): the
+ *                                   north-star's "final all-gather of limbs back to the caller's device" over NVLink
  *
  * Conventions: plain pointers and sizes only; all device pointers are raw CUDA device addresses
  * (e.g. torch.Tensor.data_ptr()); `stream` is a cudaStream_t passed as void* (NULL = legacy

@@ -231,6 +231,10 @@ class Ctx:
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
+        from gpu_fhe_b200 import shard
+        # GFHE_DEVICE_MAP=probe: the block of GPUs with the fastest host links when the box shows more GPUs than ranks
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
+        local_rank, self.device_probe = shard.choose_local_devices(local_world, local_rank)
         self.rank, self.world, self.local = rank, world, local_rank
         torch.cuda.set_device(local_rank)
         self.dev = torch.device("cuda", local_rank)
@@ -362,6 +366,7 @@ def run_b200(args, rank, world, local_rank):
     assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
     cx = Ctx(rank, world, local_rank)
     dev, st, dist = cx.dev, cx.st, cx.dist
+    local_rank = cx.local
     lib = _capi.lib
     peak, peak_src = measured_peak()
 
@@ -844,6 +849,8 @@ def run_b200(args, rank, world, local_rank):
         "cpu_baseline_vec_ops": cpu_vec,
         "gpu_launches": int(round(sum(k["launches_per_step"] for k in kernels.values()) * K)) if kernels else 3 * K,
         "clocks": clocks.summary(),
+        "devices": {"rank0_device": cx.local, "map": "probe" if cx.device_probe else "identity (device = local rank)",
+                    "probe": cx.device_probe},
         "cpu_baseline": cpu,
     }
     emit(line)

@@ -235,3 +235,80 @@ def bind_to_gpu_numa(device_index: int):
     except Exception:
         return None
     return None
+
+
+def choose_local_devices(world: int, local_rank: int, timeout_s: float = 120.0):
+    """Which GPU should the rank with this `local_rank` use when the box shows more GPUs than the job has ranks?
+
+    On this pool's 8-GPU boxes GPUs 0-3 together reach half the host-memory bandwidth of GPUs 4-7 (`_pcie_probe.py`), so a
+    4-rank job that feeds its GPUs from host memory (`poly_mul_host`) runs faster on 4-7.  Local rank 0 times the aligned
+    blocks of `world` GPUs in a subprocess (no CUDA context is created in THIS process) and leaves the answer in a file
+    named after the launcher's pid and MASTER_PORT; the other ranks read it.  Local rank 0 always writes an answer (the
+    identity map when the probe fails or times out), so the ranks cannot disagree.
+
+    Opt in with GFHE_DEVICE_MAP=probe; anything else (the default) keeps device = local_rank.  `world` is the number of
+    ranks on THIS box.  Returns (device_index, probe_result or None).
+    """
+    import json
+    import os
+    import subprocess
+    import sys
+    import tempfile
+    import time
+
+    if os.environ.get("GFHE_DEVICE_MAP", "identity") != "probe" or world <= 1:
+        return local_rank, None
+    try:
+        if torch.cuda.device_count() < 2 * world:
+            return local_rank, None
+    except Exception:
+        return local_rank, None
+    path = os.path.join(tempfile.gettempdir(), "gfhe_devmap_%d_%s.json" % (os.getppid(), os.environ.get("MASTER_PORT", "0")))
+    if local_rank == 0:
+        res = {"devices": list(range(world)), "rates": {}, "error": None}
+        try:
+            probe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_pcie_probe.py")
+            out = subprocess.run([sys.executable, probe, str(world)], capture_output=True, text=True, timeout=timeout_s)
+            if out.returncode != 0:
+                raise RuntimeError((out.stderr.strip().splitlines() or ["exit %d" % out.returncode])[-1])
+            got = json.loads(out.stdout.strip().splitlines()[-1])
+            if sorted(got["devices"]) == got["devices"] and len(got["devices"]) == world:
+                res.update(got)
+        except Exception as e:   # probe failed: identity, and say why
+            res["error"] = "%s: %s" % (type(e).__name__, e)
+        tmp = path + ".%d.tmp" % os.getpid()
+        with open(tmp, "w") as f:
+            json.dump(res, f)
+        os.replace(tmp, path)
+        import atexit
+        atexit.register(lambda: os.path.exists(path) and os.remove(path))
+        return int(res["devices"][0]), res
+    # a leftover of an earlier job under the same launcher pid and port is older than the launcher (pid reuse) or, under a
+    # long-lived launcher, describes this same box; only a map for another rank count is refused
+    deadline = time.time() + timeout_s + 60.0
+    born = _process_start_time(os.getppid())
+    while time.time() < deadline:
+        try:
+            if os.stat(path).st_mtime >= born - 1.0:
+                with open(path) as f:
+                    res = json.load(f)
+                if len(res["devices"]) == world:
+                    return int(res["devices"][local_rank]), res
+        except (OSError, ValueError, KeyError):
+            pass
+        time.sleep(0.05)
+    raise RuntimeError("choose_local_devices: local rank 0 left no device map in %s" % path)
+
+
+def _process_start_time(pid: int) -> float:
+    """Unix time at which process `pid` started (0.0 when /proc does not say)"""
+    import os
+    import time
+    try:
+        with open("/proc/%d/stat" % pid) as f:
+            ticks = int(f.read().rsplit(")", 1)[1].split()[19])      # field 22, starttime, after the "(comm)" field
+        with open("/proc/uptime") as f:
+            up = float(f.read().split()[0])
+        return time.time() - (up - ticks / os.sysconf("SC_CLK_TCK"))
+    except (OSError, ValueError, IndexError):
+        return 0.0

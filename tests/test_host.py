@@ -195,3 +195,27 @@ def test_numa_binding_helper_is_harmless_without_nvml(built_lib):
         assert os.sched_getaffinity(0) == before
     else:
         os.sched_setaffinity(0, prev)
+
+
+def test_device_map_is_identity_unless_asked_and_ranks_agree(built_lib, monkeypatch):
+    """shard.choose_local_devices: device = local rank by default and on a box without spare GPUs; with
+    GFHE_DEVICE_MAP=probe local rank 0 always leaves an answer (the identity map when the probe cannot run, as here) and the
+    other ranks read the same one."""
+    import arithmetic  # noqa: F401
+    from gpu_fhe_b200 import shard
+    monkeypatch.delenv("GFHE_DEVICE_MAP", raising=False)
+    assert shard.choose_local_devices(4, 2) == (2, None)
+    monkeypatch.setenv("GFHE_DEVICE_MAP", "probe")
+    assert shard.choose_local_devices(1, 0) == (0, None)
+    monkeypatch.setattr(shard.torch.cuda, "device_count", lambda: 4)
+    assert shard.choose_local_devices(4, 3) == (3, None)          # no second block of 4
+    monkeypatch.setattr(shard.torch.cuda, "device_count", lambda: 8)
+    monkeypatch.setenv("MASTER_PORT", "29871")
+    dev0, res0 = shard.choose_local_devices(4, 0, timeout_s=60)
+    assert res0["devices"] == [0, 1, 2, 3] or len(res0["devices"]) == 4
+    for r in (1, 2, 3):
+        dev, res = shard.choose_local_devices(4, r, timeout_s=1)
+        assert res["devices"] == res0["devices"] and dev == res0["devices"][r]
+    with pytest.raises(RuntimeError):                               # another launcher port: nobody wrote a map
+        monkeypatch.setenv("MASTER_PORT", "29872")
+        shard.choose_local_devices(4, 1, timeout_s=-59.5)

@@ -40,6 +40,8 @@ SYMBOLS = {
     "gfhe_vec_sub_u64": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_vec_mul_u64": (ctypes.c_int, [vp, u32, u32, ctypes.c_uint64, vp, vp, vp, vp]),
     "gfhe_poly_mul_pre": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
+    "gfhe_poly_mul_static": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp]),
+    "gfhe_static_workspace_bytes": (ctypes.c_size_t, []),
     "gfhe_ntt_forward_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_ntt_inverse_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp]),
     "gfhe_poly_mul_u32": (ctypes.c_int, [vp, u32, u32, u32, vp, vp, vp, vp, ctypes.c_size_t, vp]),
@@ -82,7 +84,7 @@ for _name, (_res, _args) in SYMBOLS.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 if lib.gfhe_abi_version() != ABI_VERSION:
     raise ImportError("gpufhe_b200: ABI version mismatch (library %d, binding %d)" % (lib.gfhe_abi_version(), ABI_VERSION))
 

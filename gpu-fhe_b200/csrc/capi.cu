@@ -49,6 +49,8 @@ const char* gfhe_error_string(int code) {
         case GFHE_ELAYOUT: return "packed 32-bit layout needs every modulus of the plan below 2^30";
         case GFHE_EALIGN: return "device buffer is not 16-byte aligned (transforms and products use 16-byte accesses)";
         case GFHE_EFORMAT: return "not a gpufhe_b200 plan image (bad magic, version, size or checksum)";
+        case GFHE_ESTATICWS: return "gfhe_poly_mul_static: the job needs more scratch than the library's static workspace (GFHE_STATIC_WS_BYTES = 32 MiB)";
+        case GFHE_ENOALLOC: return "gfhe_poly_mul_static: this plan runs the pipelined kernels (GFHE_PIPE=1), which allocate per stream";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown gpufhe_b200 error";
     }
 }
@@ -181,6 +183,25 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
     DeviceGuard g(P(plan)->device);
     return (int)launch_poly_mul(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b, (u64*)d_c, (u64*)d_ws, batch,
                                 S(stream));
+}
+
+static_assert(GFHE_STATIC_WS_BYTES == kStaticWsBytes, "header and library disagree on the static workspace");
+size_t gfhe_static_workspace_bytes(void) { return kStaticWsBytes; }
+
+// gfhe_poly_mul on the library's own scratch (plan.cu, g_static_ws): no cudaMalloc / cudaFree / stream or event creation
+int gfhe_poly_mul_static(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,
+                         const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_c, void* stream) {
+    if (int rc = check_range(P(plan), limb0, nl)) return rc;
+    if (!d_a || !d_b || !d_c || batch == 0) return GFHE_EARG;
+    if (P(plan)->logN == 0) return GFHE_ENOTABLES;
+    if (d_c == d_a || d_c == d_b) return GFHE_EARG;
+    if (!aligned16(d_a) || !aligned16(d_b) || !aligned16(d_c)) return GFHE_EALIGN;
+    if (P(plan)->pipe == 1) return GFHE_ENOALLOC;
+    // overflow-safe: nl * batch * N * 8 against the array
+    const unsigned long long words = (unsigned long long)nl * batch;
+    if (P(plan)->logN > 12 && words > ((unsigned long long)kStaticWsBytes / sizeof(u64)) >> P(plan)->logN) return GFHE_ESTATICWS;
+    DeviceGuard g(P(plan)->device);
+    return (int)launch_poly_mul_static(*P(plan), limb0, nl, (const u64*)d_a, (const u64*)d_b, (u64*)d_c, batch, S(stream));
 }
 
 int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t nl, uint32_t batch,

@@ -431,6 +431,34 @@ size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B) {
     return ((size_t)nl * B * sizeof(u64)) << pl.logN;   // one operand-sized scratch
 }
 
+// ---- product on the library's own scratch: an entry point that allocates nothing -----------------------------------
+// For callers that cannot call cudaMalloc (stream capture, serving loops, harnesses that forbid it): gfhe_poly_mul's
+// operand-sized workspace lives in a file-scope device array instead of a caller buffer.  Every GPU whose context loads the
+// library holds kStaticWsBytes of it until the process exits.  In host code `g_static_ws` is only the host-side stand-in of
+// the symbol: the device address is asked of the runtime once per device, with that device current, and that pointer is
+// what the kernels get.  The product writes every scratch word it later reads (the column pass of b), so nothing has to
+// start at zero; all calls on one GPU share the array, so two calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+static std::mutex g_static_mu;
+static void* g_static_addr[64];          // per device ordinal, resolved on first use
+
+cudaError_t launch_poly_mul_static(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u32 B, cudaStream_t st) {
+    if (pl.device < 0 || pl.device >= 64) return cudaErrorInvalidDevice;
+    void* ws = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mu);
+        if (!g_static_addr[pl.device]) {    // the caller holds a DeviceGuard on pl.device
+            void* p = nullptr;
+            if (cudaError_t e = cudaGetSymbolAddress(&p, g_static_ws)) return e;
+            g_static_addr[pl.device] = p;
+        }
+        ws = g_static_addr[pl.device];
+    }
+    // one stream, no two-stream split (its stream and events are created on first use) and no pipelined kernel (its
+    // synchronisation words are allocated per stream): straight to the policy's three launches
+    return do_poly_mul(pl, limb0, nl, a, b, c, (u64*)ws, B, st);
+}
+
 void host_pipe_destroy(Plan* p);   // capi.cu
 
 int plan_destroy(Plan* p) {

@@ -99,6 +99,9 @@ cudaError_t launch_poly_mul(const Plan& pl, u32 limb0, u32 nl, const u64* a, con
                             cudaStream_t st);
 size_t poly_mul_workspace_bytes(const Plan& pl, u32 nl, u32 B);
 cudaError_t launch_poly_mul_pre(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b_ntt, u64* c, u32 B, cudaStream_t st);
+// the same product on the library's file-scope scratch array (plan.cu): allocates nothing, single stream
+constexpr size_t kStaticWsBytes = (size_t)32 << 20;
+cudaError_t launch_poly_mul_static(const Plan& pl, u32 limb0, u32 nl, const u64* a, const u64* b, u64* c, u32 B, cudaStream_t st);
 // packed 32-bit layout (plans whose moduli are all below 2^30): the same operations on arrays of 32-bit words
 cudaError_t launch_ntt_fwd_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st);
 cudaError_t launch_ntt_inv_u32(const Plan& pl, u32 limb0, u32 nl, const u32* in, u32* out, u32 B, cudaStream_t st);

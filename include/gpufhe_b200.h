@@ -12,6 +12,8 @@
  *   gfhe_plan_create             <- /root/reference/primitive.py:3-4     (placeholder for the roots of unity)
  *   gfhe_poly_mul                <- /root/reference/" polynomial.py":3-5 (module that would hold poly_mul)
  *   gfhe_poly_mul_pre            <- the same product with one operand cached in the NTT domain
+ *   gfhe_poly_mul_static         <- no counterpart in the reference: gfhe_poly_mul on a static scratch array, for callers
+ *                                   that cannot allocate
  *   gfhe_ntt_mul_acc             <- /root/reference/arithmetic.py:11-13 applied in the NTT domain (sum of pointwise
  *                                   products; the reference has no NTT-domain API -- SURVEY.md section 8f row 2)
  *   gfhe_automorphism            <- absent from the reference: a(X) -> a(X^k)
@@ -43,7 +45,7 @@
 extern "C" {
 #endif
 
-#define GFHE_ABI_VERSION 5
+#define GFHE_ABI_VERSION 6
 
 #define GFHE_EARG      (-1)   /* null pointer / zero size */
 #define GFHE_ELOGN     (-2)   /* log2(N) outside [4, 20] or missing roots */
@@ -59,6 +61,8 @@ extern "C" {
 #define GFHE_ELAYOUT   (-12)  /* packed 32-bit layout asked of a plan with a modulus >= 2^30 */
 #define GFHE_EALIGN    (-13)  /* a device buffer of a transform / product call is not 16-byte aligned */
 #define GFHE_EFORMAT   (-14)  /* gfhe_plan_import: not a plan image of this library version, or corrupted */
+#define GFHE_ESTATICWS (-15)  /* gfhe_poly_mul_static: the job needs more scratch than GFHE_STATIC_WS_BYTES */
+#define GFHE_ENOALLOC  (-16)  /* gfhe_poly_mul_static: the plan runs the pipelined kernels (GFHE_PIPE=1), which allocate */
 
 typedef struct gfhe_plan* gfhe_plan_t;   /* opaque; one per (device, N, modulus chain) */
 
@@ -106,6 +110,22 @@ int gfhe_poly_mul(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t
  * polynomials by one cached operand.  No workspace.  c may alias neither input. */
 int gfhe_poly_mul_pre(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
                       const uint64_t* d_a, const uint64_t* d_b_ntt, uint64_t* d_c, void* stream);
+
+/* gfhe_poly_mul for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same product, same arguments minus the workspace: the operand-sized scratch of N > 4096 is a file-scope device array
+ * inside the library, GFHE_STATIC_WS_BYTES (32 MiB) on every GPU that loads the library, held until the process exits.
+ * A job needs num_limbs * batch * N * 8 bytes of it (N <= 4096: none); a larger job is refused with GFHE_ESTATICWS --
+ * [4, 16, 65536], the config-4 shard of one of 8 GPUs, is exactly the limit.  The call makes no cudaMalloc / cudaFree and
+ * creates no stream or event: three kernel launches on `stream` (no two-stream split); plans created under GFHE_PIPE=1
+ * are refused with GFHE_ENOALLOC.  The first call on a device resolves the array's device address (make one call before
+ * starting a stream capture).  The scratch keeps the last call's words and needs no clearing (the product overwrites
+ * every word before reading it), but ALL calls on one GPU share it: two calls that overlap on the GPU (different streams,
+ * different threads or plans) race -- order them on one stream or with events.  c may alias neither a nor b. */
+#define GFHE_STATIC_WS_BYTES ((size_t)32 << 20)
+size_t gfhe_static_workspace_bytes(void);
+int gfhe_poly_mul_static(gfhe_plan_t plan, uint32_t limb0, uint32_t num_limbs, uint32_t batch,
+                         const uint64_t* d_a, const uint64_t* d_b, uint64_t* d_c, void* stream);
 
 /* Packed 32-bit layout: the same four operations on [num_limbs, batch, N] arrays of 32-bit words (int32 / uint32
  * tensors), for plans whose moduli are ALL below 2^30 (GFHE_ELAYOUT otherwise) -- the north-star's "32-bit where the

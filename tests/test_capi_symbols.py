@@ -34,7 +34,7 @@ def test_binding_covers_header_and_abi_version(built_lib):
     import arithmetic  # noqa: F401  (loads gpu_fhe_b200)
     from gpu_fhe_b200 import _capi
     assert set(_capi.SYMBOLS) == declared_symbols()
-    assert _capi.lib.gfhe_abi_version() == _capi.ABI_VERSION == 5
+    assert _capi.lib.gfhe_abi_version() == _capi.ABI_VERSION == 6
     assert _capi.error_string(0) == "success"
     assert "2N" in _capi.error_string(-4)
 

@@ -232,7 +232,10 @@ class Ctx:
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
         from gpu_fhe_b200 import shard
-        # GFHE_DEVICE_MAP=probe: the block of GPUs with the fastest host links when the box shows more GPUs than ranks
+        # the block of GPUs with the fastest host links when the box shows at least twice as many GPUs as the job has ranks
+        # (measured: 4 ranks on GPUs 4-7 of this pool's 8-GPU boxes move host data 1.9x faster than on 0-3, e2e 7.13 ->
+        # 4.21 ms, profiles/r02_run23_*); GFHE_DEVICE_MAP=identity keeps device = local rank
+        os.environ.setdefault("GFHE_DEVICE_MAP", "probe")
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
         local_rank, self.device_probe = shard.choose_local_devices(local_world, local_rank)
         self.rank, self.world, self.local = rank, world, local_rank

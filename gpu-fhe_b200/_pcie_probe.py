@@ -3,9 +3,10 @@ every GPU, which the caller's process should not hold):
 
     python gpu-fhe_b200/_pcie_probe.py <gpus-per-block>
 
-On the 8-GPU boxes of this pool GPUs 0-3 share host links that give the four of them 115 GB/s host->device and 74 GB/s
-device->host when they copy at once, while GPUs 4-7 get 220 / 176 GB/s (profiles/r02_pcie_blocks.txt); any single GPU or pair
-gets the full 55 GB/s each.  A 4-rank job that takes GPUs 0-3 is therefore PCIe-bound at half the rate of one on 4-7.
+On the 8-GPU boxes of this pool the GPUs do not reach host memory equally (profiles/r02_run23_pcie_blocks.txt, H2D + D2H
+at once, GB/s for the whole block): four at once, GPUs 0-3 move 103 and GPUs 4-7 198; in pairs {0,1} 105, {2,3} 103,
+{4,5} 160, {6,7} 183; any single GPU 95-98.  A 4-rank job fed from host memory is therefore twice as fast on GPUs 4-7
+(bench.py e2e 7.13 -> 4.21 ms).
 The probe times every aligned block of `gpus-per-block` devices with all of its GPUs copying both ways at once and prints
 one JSON line: {"devices": [...], "rates": {"0": GB/s, "4": GB/s}}.  Block 0 is kept unless another block is at least
 10 % faster.  Only the CUDA runtime is used (ctypes); no torch import, no kernels.

@@ -717,24 +717,30 @@ def run_b200(args, rank, world, local_rank):
     a_np, b_np, c_np = (t.numpy().view(np.uint64) for t in (pa, pb, pc))
     e2e_steps = max(3, min(K, 20))
 
-    def e2e_leg(a, b, c, steps):
+    own = {}
+
+    def e2e_leg(a, b, c, steps, mod=None):
+        mod = moduli if mod is None else mod
         for _ in range(2):
-            dispatch.poly_mul_host(a, b, c, moduli, device=local_rank)
+            dispatch.poly_mul_host(a, b, c, mod, device=local_rank)
         cx.barrier()
         t0 = time.perf_counter()
         for _ in range(steps):
-            dispatch.poly_mul_host(a, b, c, moduli, device=local_rank)
-        s = cx.max_over_ranks(time.perf_counter() - t0)
-        hs = dispatch.host_stats(moduli, N, device=local_rank)
+            dispatch.poly_mul_host(a, b, c, mod, device=local_rank)
+        own["s"] = (time.perf_counter() - t0) / steps          # this rank's own time per call
+        s = cx.max_over_ranks(own["s"] * steps)
+        hs = dispatch.host_stats(mod, N, device=local_rank)
         cx.barrier()
         return s / steps, hs
     e2e_s, hs = e2e_leg(a_np, b_np, c_np, e2e_steps)
     ok = np.array_equal(c_np[0, 0], want_local[0, 0]) if rank == 0 else True
+    own_ms = own["s"] * 1e3
     # per-rank copy rates: the slowest rank's H2D / D2H stream-busy GB/s and the aggregate over ranks
     h2d_gbs, d2h_gbs = hs["h2d_bytes"] / (max(hs["h2d_ms"], 1e-6) * 1e-3) / 1e9, hs["d2h_bytes"] / (max(hs["d2h_ms"], 1e-6) * 1e-3) / 1e9
     e2e_host = {"h2d_GBs_min_rank": -cx.max_over_ranks(-h2d_gbs), "d2h_GBs_min_rank": -cx.max_over_ranks(-d2h_gbs),
                 "h2d_GBs_sum": cx.sum_over_ranks(h2d_gbs), "d2h_GBs_sum": cx.sum_over_ranks(d2h_gbs),
-                "kernel_ms_max_rank": cx.max_over_ranks(hs["kernel_ms"]), "groups": hs["groups"]}
+                "kernel_ms_max_rank": cx.max_over_ranks(hs["kernel_ms"]), "groups": hs["groups"],
+                "call_ms_fastest_rank": -cx.max_over_ranks(-own_ms), "call_ms_slowest_rank": cx.max_over_ranks(own_ms)}
     # pageable arrays (what a numpy caller of the reference holds): staged through the library's pinned ring
     pg_a, pg_b, pg_c = a_h.copy(), b_h.copy(), np.empty_like(a_h)
     pg_steps = max(3, min(K, 10))

@@ -95,5 +95,14 @@ def choose(per_block):
     return {"devices": list(range(first, first + per_block)), "rates": rates}
 
 
+def all_at_once():
+    """--all: every GPU of the box copying both ways at once (the ceiling of a job that uses all of them)"""
+    rt = _cudart()
+    n = ctypes.c_int(0)
+    _ck(rt.cudaGetDeviceCount(ctypes.byref(n)), "cudaGetDeviceCount")
+    gpus = [_Gpu(rt, d) for d in range(n.value)]
+    return {"devices": list(range(n.value)), "rates": {"all": round(block_rate(gpus), 1)}}
+
+
 if __name__ == "__main__":
-    print(json.dumps(choose(int(sys.argv[1]))), flush=True)
+    print(json.dumps(all_at_once() if "--all" in sys.argv else choose(int(sys.argv[1]))), flush=True)

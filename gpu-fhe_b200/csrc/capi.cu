@@ -2,6 +2,7 @@
 // host-buffer entry points that pipeline H2D -> kernels -> D2H over limb groups.
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstring>
@@ -459,6 +460,9 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     const size_t limb_bytes = ((size_t)batch * sizeof(u64)) << pl->logN;
     // limb groups of ~32 MiB per operand: large enough for full PCIe rate, small enough to overlap
     size_t group_mib = 32;
+    // a job of a few large limbs (at most 32 MiB per operand: the config-4 shard of one of 8 GPUs is 4 limbs of 8 MiB) would be
+    // 3 groups; 4 MiB groups cut its batch into 8 (measured on 8 ranks: 5.22 -> 5.03 ms per call, profiles/r02_run26_groups_n8.txt)
+    if (limb_bytes * pl->L <= ((size_t)32 << 20)) group_mib = 4;
     if (const char* env = std::getenv("GFHE_HOST_GROUP_MIB")) { const long v = std::atol(env); if (v >= 1 && v <= 4096) group_mib = (size_t)v; }
     u32 gl = (u32)(((group_mib << 20) + limb_bytes - 1) / limb_bytes);
     if (gl < 1) gl = 1;
@@ -473,12 +477,25 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     const size_t limb_elems = (size_t)batch << pl->logN;
     // group schedule: full groups, then a halving tail (gl/2, gl/4, ..., 1) so that what is left after the last H2D
     // copy -- the last group's kernels and its D2H copy -- is one limb's worth, not a full group's
-    std::vector<u32> groups, first;
-    {
+    // A group size below one limb's bytes cuts every limb's batch instead (a small shard -- 4 limbs on one of 8 GPUs -- is
+    // otherwise 3 groups, and the pipeline's fill and drain are most of the call).
+    struct Group { u32 l0, nl, b0, nb; };
+    std::vector<Group> groups;
+    const u32 parts = (u32)std::min<size_t>(batch, (limb_bytes + (group_mib << 20) - 1) / (group_mib << 20));
+    if (parts >= 2) {
+        for (u32 l = 0; l < pl->L; ++l)
+            for (u32 k = 0; k < parts; ++k) {
+                const u32 b0 = (u32)((u64)batch * k / parts), b1 = (u32)((u64)batch * (k + 1) / parts);
+                groups.push_back({l, 1u, b0, b1 - b0});
+            }
+    } else {
         u32 left = pl->L, l0 = 0;
-        while (left > gl) { groups.push_back(gl); first.push_back(l0); l0 += gl; left -= gl; }
-        for (u32 gsz = left; left > 0;) { gsz = gsz > 1 ? (gsz + 1) / 2 : 1; if (gsz > left) gsz = left; groups.push_back(gsz); first.push_back(l0); l0 += gsz; left -= gsz; }
+        while (left > gl) { groups.push_back({l0, gl, 0u, batch}); l0 += gl; left -= gl; }
+        for (u32 gsz = left; left > 0;) { gsz = gsz > 1 ? (gsz + 1) / 2 : 1; if (gsz > left) gsz = left; groups.push_back({l0, gsz, 0u, batch}); l0 += gsz; left -= gsz; }
     }
+    const size_t poly_elems = (size_t)1 << pl->logN, poly_bytes = sizeof(u64) << pl->logN;
+    auto g_off = [&](const Group& g) { return limb_elems * g.l0 + poly_elems * g.b0; };          // words from the start of a host operand
+    auto g_bytes = [&](const Group& g) { return poly_bytes * g.nb * g.nl; };
     HostPipe* hp = nullptr;
     cudaError_t e = host_pipe_get(pl, limb_bytes * gl, op == 2, staged, groups.size(), &hp);
     if (e) return (int)e;
@@ -502,7 +519,7 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
                 const int slot = (int)(g2 % kS);
                 if (cudaError_t de = cudaEventSynchronize(hp->out_done[slot])) { drain_err.store((int)de); return; }
                 const double t0 = now_ms();
-                par_memcpy(h_c + limb_elems * first[g2], hp->pin[slot][2], limb_bytes * groups[g2], out_thr);
+                par_memcpy(h_c + g_off(groups[g2]), hp->pin[slot][2], g_bytes(groups[g2]), out_thr);
                 stage_out_ms += now_ms() - t0;
                 drained.store(g2 + 1, std::memory_order_release);
             }
@@ -510,8 +527,8 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
     auto body = [&]() -> cudaError_t {
         for (size_t it = 0; it < groups.size(); ++it) {
             const int slot = (int)(it % kS);
-            const u32 nl = groups[it], l0 = first[it];
-            const size_t bytes = limb_bytes * nl, off = limb_elems * l0;
+            const u32 nl = groups[it].nl, l0 = groups[it].l0, nb = groups[it].nb;
+            const size_t bytes = g_bytes(groups[it]), off = g_off(groups[it]);
             u64 *da = hp->buf[slot][0], *db = hp->buf[slot][1], *dc = hp->buf[slot][2], *dw = hp->buf[slot][3];
             const u64 *src_a = h_a + off, *src_b = h_b ? h_b + off : nullptr;
             u64* dst_c = h_c + off;
@@ -539,9 +556,9 @@ static int run_host(Plan* pl, int op, u32 batch, const u64* h_a, const u64* h_b,
             if ((e = cudaEventRecord(hp->in_done[slot], hp->s_in))) return e;
             if ((e = cudaStreamWaitEvent(hp->s_run, hp->in_done[slot], 0))) return e;
             if ((e = cudaEventRecord(tv[2], hp->s_run))) return e;
-            if (op == 0) e = launch_ntt_fwd(*pl, l0, nl, da, dc, batch, hp->s_run);
-            else if (op == 1) e = launch_ntt_inv(*pl, l0, nl, da, dc, batch, hp->s_run);
-            else e = launch_poly_mul(*pl, l0, nl, da, db, dc, dw, batch, hp->s_run);
+            if (op == 0) e = launch_ntt_fwd(*pl, l0, nl, da, dc, nb, hp->s_run);
+            else if (op == 1) e = launch_ntt_inv(*pl, l0, nl, da, dc, nb, hp->s_run);
+            else e = launch_poly_mul(*pl, l0, nl, da, db, dc, dw, nb, hp->s_run);
             if (e) return e;
             if ((e = cudaEventRecord(tv[3], hp->s_run))) return e;
             if ((e = cudaEventRecord(hp->run_done[slot], hp->s_run))) return e;

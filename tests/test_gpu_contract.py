@@ -258,6 +258,40 @@ def test_host_path_pageable_and_pinned(cuda_device):
         del os.environ["GFHE_HOST_GROUP_MIB"]
 
 
+def test_host_path_groups_smaller_than_a_limb(cuda_device):
+    """A group size below one limb's bytes cuts every limb's batch (small shards: more pipeline stages than limbs);
+    uneven cuts (batch 5 in 3 parts), pinned and pageable callers, product and both transforms."""
+    import primitive as P
+    from gpu_fhe_b200 import dispatch
+    N, L, B = 65536, 3, 5             # 2.5 MiB per limb, groups of 1 MiB: 3 parts of 1, 2, 2 polynomials per limb
+    moduli = P.ntt_primes(60, L)
+    a, b = rand_lbn(5, moduli, B, N), rand_lbn(6, moduli, B, N)
+    R = oracle_ring(N, moduli)
+    want = R.poly_mul(a, b, fast=True, nthreads=16)
+    os.environ["GFHE_HOST_GROUP_MIB"] = "1"
+    try:
+        out = np.zeros_like(a)
+        dispatch.poly_mul_host(a, b, out, moduli, device=cuda_device.index)
+        st = dispatch.host_stats(moduli, N, device=cuda_device.index)
+        assert np.array_equal(out, want)
+        assert st["groups"] == 9 and st["staged"] == 1.0 and st["h2d_bytes"] == 2 * a.nbytes and st["d2h_bytes"] == a.nbytes
+        pa = torch.from_numpy(a.view(np.int64)).pin_memory()
+        pb = torch.from_numpy(b.view(np.int64)).pin_memory()
+        pc = torch.zeros_like(pa).pin_memory()
+        dispatch.poly_mul_host(pa.numpy().view(np.uint64), pb.numpy().view(np.uint64), pc.numpy().view(np.uint64), moduli,
+                               device=cuda_device.index)
+        st = dispatch.host_stats(moduli, N, device=cuda_device.index)
+        assert np.array_equal(pc.numpy().view(np.uint64), want) and st["groups"] == 9 and st["staged"] == 0.0
+        X = np.zeros_like(a)
+        dispatch.ntt_host(a, X, moduli, device=cuda_device.index)
+        assert np.array_equal(X, R.ntt(a, fast=True, nthreads=16))
+        back = np.zeros_like(a)
+        dispatch.ntt_host(X, back, moduli, inverse=True, device=cuda_device.index)
+        assert np.array_equal(back, a)
+    finally:
+        del os.environ["GFHE_HOST_GROUP_MIB"]
+
+
 # ---------------------------------------------------------------------------------------------------
 # more than one GPU in the process / on the box
 # ---------------------------------------------------------------------------------------------------

@@ -243,7 +243,7 @@ def choose_local_devices(world: int, local_rank: int, timeout_s: float = 120.0):
     On this pool's 8-GPU boxes GPUs 0-3 together reach half the host-memory bandwidth of GPUs 4-7 (`_pcie_probe.py`), so a
     4-rank job that feeds its GPUs from host memory (`poly_mul_host`) runs faster on 4-7.  Local rank 0 times the aligned
     blocks of `world` GPUs in a subprocess (no CUDA context is created in THIS process) and leaves the answer in a file
-    named after the launcher's pid and MASTER_PORT; the other ranks read it.  Local rank 0 always writes an answer (the
+    named after MASTER_PORT in the temporary directory; the other ranks read it.  Local rank 0 always writes an answer (the
     identity map when the probe fails or times out), so the ranks cannot disagree.
 
     Opt in with GFHE_DEVICE_MAP=probe; anything else (the default) keeps device = local_rank.  `world` is the number of
@@ -263,8 +263,12 @@ def choose_local_devices(world: int, local_rank: int, timeout_s: float = 120.0):
             return local_rank, None
     except Exception:
         return local_rank, None
-    path = os.path.join(tempfile.gettempdir(), "gfhe_devmap_%d_%s.json" % (os.getppid(), os.environ.get("MASTER_PORT", "0")))
+    path = os.path.join(tempfile.gettempdir(), "gfhe_devmap_%s.json" % os.environ.get("MASTER_PORT", "0"))
     if local_rank == 0:
+        try:
+            os.remove(path)                       # a crashed earlier job's answer
+        except OSError:
+            pass
         res = {"devices": list(range(world)), "rates": {}, "error": None}
         try:
             probe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_pcie_probe.py")
@@ -280,16 +284,14 @@ def choose_local_devices(world: int, local_rank: int, timeout_s: float = 120.0):
         with open(tmp, "w") as f:
             json.dump(res, f)
         os.replace(tmp, path)
-        import atexit
-        atexit.register(lambda: os.path.exists(path) and os.remove(path))
         return int(res["devices"][0]), res
-    # a leftover of an earlier job under the same launcher pid and port is older than the launcher (pid reuse) or, under a
-    # long-lived launcher, describes this same box; only a map for another rank count is refused
+    # the ranks of one job start within a moment of each other and local rank 0 writes its answer after that; a file older
+    # than this process (less a margin) is a crashed earlier job's on the same port
     deadline = time.time() + timeout_s + 60.0
-    born = _process_start_time(os.getppid())
+    born = _process_start_time(os.getpid())
     while time.time() < deadline:
         try:
-            if os.stat(path).st_mtime >= born - 1.0:
+            if os.stat(path).st_mtime >= born - 2.0:
                 with open(path) as f:
                     res = json.load(f)
                 if len(res["devices"]) == world:

@@ -219,3 +219,6 @@ def test_device_map_is_identity_unless_asked_and_ranks_agree(built_lib, monkeypa
     with pytest.raises(RuntimeError):                               # another launcher port: nobody wrote a map
         monkeypatch.setenv("MASTER_PORT", "29872")
         shard.choose_local_devices(4, 1, timeout_s=-59.5)
+    import os
+    import tempfile
+    os.remove(os.path.join(tempfile.gettempdir(), "gfhe_devmap_29871.json"))

@@ -184,6 +184,31 @@ def test_partition():
     assert sorted((x.limb_ids, x.batch) for x in s) == sorted(((i,), (2 * j, 2 * j + 2)) for i in range(2) for j in range(4))
 
 
+def test_device_map_exchange_between_concurrent_processes(built_lib, tmp_path):
+    """Four processes started together, the way a launcher starts ranks (local rank 0 last, and it may finish before the
+    others have looked): all four must come back with the same map."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, json; sys.path.insert(0, %r)\n"
+        "import arithmetic\n"
+        "from gpu_fhe_b200 import shard\n"
+        "shard.torch.cuda.device_count = lambda: 8\n"
+        "r = int(sys.argv[1])\n"
+        "dev, res = shard.choose_local_devices(4, r, timeout_s=30)\n"
+        "print(json.dumps([r, dev, res['devices']]))\n" % root)
+    env = dict(os.environ, GFHE_DEVICE_MAP="probe", MASTER_PORT="29873", TMPDIR=str(tmp_path))
+    procs = [subprocess.Popen([sys.executable, "-c", code, str(r)], env=env, stdout=subprocess.PIPE, text=True) for r in (3, 2, 1, 0)]
+    outs = [json.loads(p.communicate(timeout=120)[0].strip().splitlines()[-1]) for p in procs]
+    assert all(p.returncode == 0 for p in procs)
+    maps = {tuple(o[2]) for o in outs}
+    assert len(maps) == 1 and all(o[1] == o[2][o[0]] for o in outs)
+    assert sorted(o[1] for o in outs) == list(maps.pop())
+
+
 def test_numa_binding_helper_is_harmless_without_nvml(built_lib):
     """shard.bind_to_gpu_numa returns None (and changes nothing) when NVML has no device to ask."""
     import os
